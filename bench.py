@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path (BASELINE.json): frames/s and achieved HBM GB/s of the fused
+argmax + per-label statistics over batched 513x513x21 u8 logits, per GPU count, with the reference
+CPU post-processing timed beside it.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # our arm (one rank per GPU)
+    python bench.py --impl reference [--gpus N] [--steps K] ...    # CPU arm (oracle port, all cores)
+
+A step = one pass of the hot path over one batch of synthetic logits: BASELINE config 2
+(batch 64 of 513x513x21 u8 per GPU, 16:9 ROI 288x513); frames shard by GPU, no collective on the
+data path (weak scaling).  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+H, W, C = 513, 513, 21
+ROI_H, ROI_W = 288, 513                      # 1920x1080 camera, keep-aspect (sem_seg_server.py:164)
+BATCH = 64                                   # frames per GPU per step (config 2)
+N_ROTATE = 4                                 # distinct batches cycled through (4 x 354 MB >> 126 MB L2)
+ALGO_BYTES_PER_FRAME = H * W * C + H * W + C * 4 * 8      # logits read + label map + stats written
+METRIC = "frames/sec (513x513x21 u8 logits -> label map + per-label stats)"
+WORKLOAD = "config2: batch 64 x 513x513x21 u8 logits per GPU, argmax + segment stats, ROI 288x513"
+
+
+def synth_batch(seed, n=BATCH):
+    """iid-uniform u8 logits (SURVEY §8d set U0); regenerable on the CPU for spot checks."""
+    return np.random.default_rng(seed).integers(0, 256, (n, H, W, C), dtype=np.uint8)
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.idx, self.rows, self._stop_evt, self.proc = gpu_index, [], threading.Event(), None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+                if self._stop_evt.is_set():
+                    break
+        except Exception:
+            pass
+
+    def stop(self):
+        self._stop_evt.set()
+        if self.proc:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_threads():
+    return len(os.sched_getaffinity(0))
+
+
+def time_cpu_port(batch_np, threads, min_seconds, max_passes=1000):
+    """Oracle C port (oracle/segpath_c.c), frames sharded over `threads` host threads."""
+    from oracle import cport
+    cport.argmax_stats(batch_np[:max(1, threads)], ROI_H, ROI_W, threads=threads)   # warm (page in, build)
+    passes, t0 = 0, time.perf_counter()
+    while True:
+        cport.argmax_stats(batch_np, ROI_H, ROI_W, threads=threads)
+        passes += 1
+        el = time.perf_counter() - t0
+        if el >= min_seconds or passes >= max_passes:
+            return passes * batch_np.shape[0] / el, passes, el
+
+
+def run_reference(args):
+    """CPU arm: the reference has no compiled code (100% Python over numpy/PIL/OpenCV) and cannot
+    travel to the GPU box, so this times the oracle port of the same path on all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = cpu_threads()
+    batch = synth_batch(1000)
+    from oracle import cport
+    for _ in range(max(1, args.warmup)):
+        cport.argmax_stats(batch[:threads], ROI_H, ROI_W, threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cport.argmax_stats(batch, ROI_H, ROI_W, threads=threads)
+    el = time.perf_counter() - t0
+    fps = args.steps * BATCH / el
+    sample = "%d steps x one %d-frame batch, C port of np.argmax+bincount stats, %d threads" % (
+        args.steps, BATCH, threads)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "l2": "n/a (CPU)"},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ssb(args):
+    import torch
+    import torch.distributed as dist
+    import ssb200
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (args.gpus, world))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- synthetic inputs, resident in HBM before the timed region -------------------------------
+    host_batches = [synth_batch(1000 * rank + i) for i in range(N_ROTATE)]
+    dev_batches = [torch.from_numpy(b).cuda() for b in host_batches]
+    labels = torch.empty((BATCH, H, W), dtype=torch.uint8, device="cuda")
+    stats = torch.empty((BATCH, C, 4), dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream()
+
+    def step(i):
+        ssb200.argmax_stats(dev_batches[i % N_ROTATE], ROI_H, ROI_W, labels=labels, stats=stats, stream=stream)
+
+    for i in range(max(3, args.warmup)):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for i in range(args.steps):
+        step(i)
+    ev1.record(stream)
+    barrier()
+    dev_ms = ev0.elapsed_time(ev1)
+    if sampler and dev_ms < 1500:          # keep the GPU under the same load long enough for nvidia-smi to see it
+        t_end = time.time() + 1.5
+        i = 0
+        while time.time() < t_end:
+            step(i); i += 1
+            if i % 64 == 0:
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler else None
+
+    # ---- parity spot check of what was just timed (oracle as checker) ------------------------------
+    from oracle import cport
+    last = (args.steps - 1) % N_ROTATE
+    step(last)
+    torch.cuda.synchronize()
+    want_l, want_s = cport.argmax_stats(host_batches[last][:2], ROI_H, ROI_W, threads=2)
+    ok = bool((labels[:2].cpu().numpy() == want_l).all() and
+              (stats[:2].cpu().numpy().view(np.uint64) == want_s).all())
+    if not ok:
+        raise SystemExit("bench: GPU result differs from the oracle")
+
+    # ---- end to end through the C-ABI with HOST buffers (pinned), H2D + D2H inside the timed region --
+    pinned = [torch.from_numpy(b).pin_memory() for b in host_batches[:2]]
+    pipe = ssb200.HostPipeline(H, W, C, np.uint8, frames_per_chunk=16, n_slots=3, device=local)
+    out_labels = torch.empty((BATCH, H, W), dtype=torch.uint8).pin_memory().numpy()
+    out_stats = torch.empty((BATCH, C, 4), dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+    e2e_steps = max(3, min(args.steps, 10))
+    for i in range(2):
+        pipe.argmax_stats(pinned[i % 2].numpy(), ROI_H, ROI_W, labels_out=out_labels, stats_out=out_stats)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        pipe.argmax_stats(pinned[i % 2].numpy(), ROI_H, ROI_W, labels_out=out_labels, stats_out=out_stats)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    want_l, want_s = cport.argmax_stats(host_batches[(e2e_steps - 1) % 2][-1:], ROI_H, ROI_W)
+    if not ((out_labels[-1:] == want_l).all() and (out_stats[-1:] == want_s).all()):
+        raise SystemExit("bench: e2e result differs from the oracle")
+    pipe.close()
+
+    # ---- max over ranks ------------------------------------------------------------------------------
+    times = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(times[0]), float(times[1])
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        frames = world * BATCH * args.steps
+        fps = frames / (dev_ms * 1e-3)
+        launch_s = dev_ms * 1e-3 / args.steps                    # one kernel launch per step and GPU
+        achieved = ALGO_BYTES_PER_FRAME * BATCH / launch_s / 1e9
+        e2e_fps = world * BATCH * e2e_steps / (e2e_ms * 1e-3)
+        threads = cpu_threads()
+        cpu_fps, passes, cpu_el = time_cpu_port(host_batches[0], threads, min_seconds=10.0)
+        t1 = time.perf_counter()
+        from oracle import segpath as sp
+        sp.argmax_stats(host_batches[0][:2], ROI_H, ROI_W)
+        numpy_fps = 2 / (time.perf_counter() - t1)
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic_per_launch.json")   # from the ncu --set full capture
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("argmax_stats_u8_b64_bytes")
+            except Exception:
+                traffic = None
+        print(json.dumps({
+            "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frames_per_gpu_per_step": BATCH,
+                       "l2": "inputs larger than L2: %d distinct 354 MB batches rotated, no flush" % N_ROTATE,
+                       "sharding": "frames by GPU, no collective"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "kernel": "argmax_stats_u8_kernel<21,...>",
+                         "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH,
+                         "frac_of_nominal_8TBs": achieved / 8000.0},
+            "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": threads, "kind": "port",
+                             "sample": "%d passes over one %d-frame batch in %.1f s, C port, %d threads; "
+                                       "numpy restatement 1 thread: %.1f frames/s" % (passes, BATCH, cpu_el, threads,
+                                                                                       numpy_fps)},
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": BATCH * H * W * C,
+                    "d2h_bytes_per_step": BATCH * (H * W + C * 32), "steps": e2e_steps,
+                    "api": "ssb_pipeline_argmax_stats_host (pinned host buffers, 3 streams x 16-frame chunks)"},
+            "gpu_launches": world * args.steps,
+            "clocks": clocks,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ssb", choices=["ssb", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ssb(args)
+
+
+if __name__ == "__main__":
+    main()

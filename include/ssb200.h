@@ -1,0 +1,135 @@
+/*
+ * ssb200 -- C-ABI of the B200-native segmentation hot path.
+ *
+ * Drop-in boundary for the per-frame data-parallel path of goruck/semantic-segmentation-server
+ * (reference: /root/reference/sem_seg_server.py).  The reference has no plugin/FFI interface of its
+ * own for this path; the seam is the body of `recognize_and_segment` (sem_seg_server.py:135-213).
+ * Each entry point below names the reference lines it replaces.  A Python maintainer binds these
+ * with ctypes; nothing in the signatures is a torch or C++ type.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
+ *   - the caller owns every buffer; the library allocates nothing persistent in the device-pointer
+ *     entry points and zeroes `stats` itself on the given stream;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*, 0 = legacy default stream)
+ *     of the CURRENT device; calls are asynchronous with respect to the host and never
+ *     synchronise the device; re-entrant across (device, stream) pairs;
+ *   - return value: SSB_OK (0) or a negative SSB_ERR_* code; a thread-local message is available
+ *     from ssb_last_error().  Nothing throws or aborts across the ABI.
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     SSB_ERR_CUDA.
+ */
+#ifndef SSB200_H_
+#define SSB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSB_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define SSB_API __attribute__((visibility("default")))
+#else
+#define SSB_API
+#endif
+
+#define SSB_OK 0
+#define SSB_ERR_BAD_SHAPE (-1)  /* non-positive / inconsistent dimensions, ROI outside the frame */
+#define SSB_ERR_BAD_POINTER (-2) /* NULL where a buffer is required */
+#define SSB_ERR_LIMIT (-3)      /* documented size limit exceeded */
+#define SSB_ERR_CUDA (-4)       /* a CUDA runtime call failed (message has the CUDA error string) */
+
+/* Statistics block per frame: stats[b][c][SSB_STAT_*], unsigned 64-bit.
+ *   N  = pixels of label c inside the ROI          (len(mask_img), sem_seg_server.py:111)
+ *   SX = sum of column indices x of those pixels    (m10 of sem_seg_server.py:115-121, as a pixel sum)
+ *   SY = sum of row indices y                       (m01 of sem_seg_server.py:115-122)
+ *   SQ = sum of the winning logit: raw u8 q for the u8 entry point; value * 2^24 as a
+ *        two's-complement int64 for the fp16 entry point (exact, order-independent). */
+#define SSB_STAT_N 0
+#define SSB_STAT_SX 1
+#define SSB_STAT_SY 2
+#define SSB_STAT_SQ 3
+#define SSB_F16_FIXED_SHIFT 24
+
+SSB_API int ssb_version(void);
+
+/* Message for the last non-zero status returned to the calling thread ("" if none). */
+SSB_API const char *ssb_last_error(void);
+
+/* Replaces sem_seg_server.py:150-161 (cvtColor BGR2RGB -> Image.fromarray -> edgetpu
+ * resampling_with_original_ratio(NEAREST) -> np.asarray().flatten()) for a batch of frames.
+ *
+ *   frames_bgr   [B][Hc][Wc][3] u8, frame b at frames_bgr + b*frame_stride (bytes, >= Hc*Wc*3)
+ *   xtab, ytab   int32[new_w], int32[new_h]: source column / row of each destination column / row
+ *                (Pillow's accumulated-double NEAREST tables, built on the host by the caller --
+ *                 semseg host module `nearest_index_table`; values in [0,Wc) / [0,Hc))
+ *   out_rgb      [B][H][W][3] u8, dense; pixels with x >= new_w or y >= new_h are zero
+ *                (ImageOps.expand padding).  new_w <= W, new_h <= H.
+ * The stretch branch (sem_seg_server.py:157-159) is the same call with new_w = W, new_h = H. */
+SSB_API int ssb_preprocess_nearest_u8(const uint8_t *frames_bgr, int B, int Hc, int Wc, int64_t frame_stride,
+                              const int32_t *xtab, const int32_t *ytab, int new_w, int new_h,
+                              uint8_t *out_rgb, int H, int W, void *stream);
+
+/* Replaces the ArgMax tail of engine.run_inference (sem_seg_server.py:162), the reshape / crop /
+ * astype of :163-170 and the counting + moment arithmetic of :102-122, per label, in one pass.
+ *
+ *   logits       [B][H][W][C] u8 quantised class scores (dequantisation s*(q-zp), s>0, is monotone,
+ *                so argmax on q is exact)
+ *   roi_h, roi_w crop of :164-167: statistics cover rows < roi_h and columns < roi_w only;
+ *                1 <= roi_h <= H, 1 <= roi_w <= W
+ *   labels       [B][H][W] u8 label map (first index of the maximum, np.argmax semantics), written
+ *                for the FULL frame; may be NULL to skip it
+ *   stats        [B][C][4] u64, zeroed by the call, then accumulated
+ * Limits: 2 <= C <= 255 (the fast path is compiled for C = 19 and C = 21), H*W < 2^31,
+ *         B*H*W < 2^40.  The fast path needs `logits` 16-byte aligned and `labels` 4-byte aligned
+ *         (any torch allocation; a frame offset that is a multiple of 16 frames keeps both); other
+ *         shapes/alignments take a slower generic kernel with identical results. */
+SSB_API int ssb_argmax_stats_u8(const uint8_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
+                        uint8_t *labels, uint64_t *stats, void *stream);
+
+/* Same contract for IEEE fp16 logits (Cityscapes-shaped config).  `logits` is [B][H][W][C] of
+ * 16-bit halves passed as uint16_t bit patterns.  Comparison is the floating-point `>` (so
+ * -0 == +0 and the first index wins); inputs must be NaN-free (a NaN never wins here, numpy
+ * lets the first NaN win).  SQ accumulates value * 2^24 exactly; +-inf winners are not supported
+ * in SQ (labels and N/SX/SY stay exact). */
+SSB_API int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
+                         uint8_t *labels, uint64_t *stats, void *stream);
+
+/* Replaces sem_seg_server.py:173 (label_to_color_image) + :79-85 (blur 3x3, BGR2GRAY, threshold
+ * 127) -- the foreground mask handed to cv2.findContours -- with the exact integer formula.
+ *
+ *   labels       [B][H][W] u8 label map (as written by ssb_argmax_stats_*)
+ *   colormap     [256][3] u8 (PASCAL VOC colormap, sem_seg_server.py:36-50)
+ *   mask         [B][H][W] u8: 255 where foreground inside the ROI, 0 elsewhere (also outside the
+ *                ROI).  Border handling is BORDER_REFLECT_101 on the cropped roi_h x roi_w image. */
+SSB_API int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int roi_h, int roi_w,
+                   const uint8_t *colormap, uint8_t *mask, void *stream);
+
+/* Host-buffer convenience for callers that hold frames/logits in host memory (the reference's
+ * situation: cap.read() and engine.run_inference both return host arrays).
+ *
+ * An ssb_pipeline owns pinned staging buffers, device buffers and CUDA streams for up to
+ * `max_frames_per_chunk` frames per chunk on the current device, created once and reused; the
+ * _host call splits the batch into chunks, overlaps host->device copies with the kernels and
+ * device->host copies of the results, and returns when `stats_host` (and `labels_host`) are
+ * complete.  Host pointers may be pageable; pinned memory (cudaHostAlloc / torch pin_memory) is
+ * copied at full PCIe speed. */
+typedef struct ssb_pipeline ssb_pipeline;
+
+SSB_API int ssb_pipeline_create(ssb_pipeline **out, int H, int W, int C, int elem_bytes /*1=u8, 2=f16*/,
+                        int max_frames_per_chunk, int n_slots);
+SSB_API int ssb_pipeline_destroy(ssb_pipeline *p);
+
+/* logits_host [B][H][W][C]; labels_host [B][H][W] or NULL; stats_host [B][C][4] u64.
+ * Replaces sem_seg_server.py:162-181 for a batch of frames held on the host. */
+SSB_API int ssb_pipeline_argmax_stats_host(ssb_pipeline *p, const void *logits_host, int B, int roi_h, int roi_w,
+                                   uint8_t *labels_host, uint64_t *stats_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSB200_H_ */

@@ -1,0 +1,270 @@
+"""Host side of the hot path: mirrors the functions of the reference's `sem_seg_server.py` that sit
+on the per-frame path, with the heavy lifting done by libssb200 (CUDA, sm_100a) through the C-ABI.
+
+Names, argument meaning and error behaviour follow the reference where a counterpart exists:
+    load_labels                     sem_seg_server.py:30-34
+    create_pascal_label_colormap    sem_seg_server.py:36-50
+    SegmentContour, Centroid        sem_seg_server.py:21-25
+    preprocess_frames               sem_seg_server.py:150-161   (K1, batched, on device)
+    argmax_stats                    sem_seg_server.py:162-170 + 102-122 (K2+K3, batched, on device)
+    foreground_mask                 sem_seg_server.py:173 + 79-85 (device)
+    objects_from_stats              sem_seg_server.py:92-133 + 183-192 restated per label
+    objects_from_contours           sem_seg_server.py:77-133 + 183-192, reference-literal (cv2 on the
+                                    GPU-made mask; the polygon area/moment step stays on the CPU)
+PyTorch is used for device memory and streams only.
+"""
+import collections
+import re
+
+import numpy as np
+import torch
+
+from . import _cabi
+
+SegmentContour = collections.namedtuple("SegmentContour", ["label", "score", "area", "centroid"])
+
+
+class Centroid(collections.namedtuple("Centroid", ["cx", "cy"])):
+    __slots__ = ()
+
+
+def load_labels(path):
+    """{int: name} from '<int> <name>' lines (sem_seg_server.py:30-34)."""
+    pat = re.compile(r"\s*(\d+)(.+)")
+    with open(path, "r", encoding="utf-8") as f:
+        pairs = (pat.match(line).groups() for line in f.readlines())
+        return {int(num): text.strip() for num, text in pairs}
+
+
+def create_pascal_label_colormap():
+    """256x3 PASCAL VOC colormap (sem_seg_server.py:36-50), vectorised over labels."""
+    idx = np.arange(256, dtype=np.int64)
+    cmap = np.zeros((256, 3), dtype=np.int64)
+    for shift in range(7, -1, -1):
+        for ch in range(3):
+            cmap[:, ch] |= ((idx >> ch) & 1) << shift
+        idx = idx >> 3
+    return cmap
+
+
+def foreground_label_set(num_classes, colormap=None):
+    """Labels whose uniform colour passes the reference's threshold (sem_seg_server.py:82-85):
+    BGR2GRAY fixed-point luma of the RGB colour, > 127.  {7, 15} for the 21 VOC classes."""
+    cm = create_pascal_label_colormap() if colormap is None else colormap
+    gray = (cm[:, 0] * 1868 + cm[:, 1] * 9617 + cm[:, 2] * 4899 + 8192) >> 14
+    return {int(l) for l in range(num_classes) if gray[l] > 127}
+
+
+# ---- geometry (host scalars; sem_seg_server.py:139-141,155,164) ---------------------------------
+def nearest_index_table(n_in, n_out):
+    """Pillow NEAREST source indices: position accumulated in double from scale/2, truncated."""
+    if n_in <= 0 or n_out <= 0:
+        raise ValueError("empty axis")
+    scale = n_in / n_out
+    tab = np.empty(n_out, dtype=np.int32)
+    pos = scale / 2.0
+    for i in range(n_out):
+        tab[i] = int(pos)
+        pos += scale
+    return tab
+
+
+class FrameGeometry:
+    """Everything the kernels need to know about one camera size / model input size pair."""
+
+    def __init__(self, cam_w, cam_h, width, height, keep_aspect_ratio=True):
+        self.cam_w, self.cam_h, self.width, self.height = cam_w, cam_h, width, height
+        if keep_aspect_ratio:
+            # edgetpu resampling_with_original_ratio, call site sem_seg_server.py:155-156
+            r = min(width / cam_w, height / cam_h)
+            self.new_w, self.new_h = int(cam_w * r), int(cam_h * r)
+            if self.new_w <= 0 or self.new_h <= 0:
+                raise ValueError("frame collapses to zero pixels")
+            self.ratio = (self.new_w / width, self.new_h / height)
+        else:
+            self.new_w, self.new_h, self.ratio = width, height, (1.0, 1.0)   # :157-159
+        # crop applied to the model output, by the reference's formula (:164)
+        self.roi_w, self.roi_h = int(width * self.ratio[0]), int(height * self.ratio[1])
+        self.xtab = nearest_index_table(cam_w, self.new_w)
+        self.ytab = nearest_index_table(cam_h, self.new_h)
+        self._dev_tabs = {}
+
+    def device_tables(self, device):
+        key = str(device)
+        if key not in self._dev_tabs:
+            self._dev_tabs[key] = (torch.from_numpy(self.xtab).to(device), torch.from_numpy(self.ytab).to(device))
+        return self._dev_tabs[key]
+
+
+def _stream_ptr(stream):
+    s = torch.cuda.current_stream() if stream is None else stream
+    return s.cuda_stream
+
+
+def _require_cuda(t, name):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.is_contiguous()):
+        raise ValueError("%s must be a contiguous CUDA tensor (there is no CPU path)" % name)
+
+
+# ---- K1 -------------------------------------------------------------------------------------------
+def preprocess_frames(frames_bgr, geom, out=None, stream=None):
+    """[B,Hc,Wc,3] u8 BGR camera frames (device) -> [B,H,W,3] u8 RGB model input (device).
+
+    Replaces sem_seg_server.py:150-161 for a batch; `geom` is a FrameGeometry.  Returns `out`."""
+    _require_cuda(frames_bgr, "frames_bgr")
+    if frames_bgr.dtype != torch.uint8 or frames_bgr.dim() != 4 or frames_bgr.shape[3] != 3:
+        raise ValueError("frames_bgr must be [B,Hc,Wc,3] uint8")
+    b, hc, wc, _ = frames_bgr.shape
+    if (wc, hc) != (geom.cam_w, geom.cam_h):
+        raise ValueError("frames are %dx%d, geometry is for %dx%d" % (wc, hc, geom.cam_w, geom.cam_h))
+    if out is None:
+        out = torch.empty((b, geom.height, geom.width, 3), dtype=torch.uint8, device=frames_bgr.device)
+    _require_cuda(out, "out")
+    xt, yt = geom.device_tables(frames_bgr.device)
+    with torch.cuda.device(frames_bgr.device):
+        _cabi.check(_cabi.lib.ssb_preprocess_nearest_u8(
+            frames_bgr.data_ptr(), b, hc, wc, hc * wc * 3, xt.data_ptr(), yt.data_ptr(), geom.new_w, geom.new_h,
+            out.data_ptr(), geom.height, geom.width, _stream_ptr(stream)))
+    return out
+
+
+# ---- K2 + K3 ----------------------------------------------------------------------------------------
+def argmax_stats(logits, roi_h=None, roi_w=None, labels=None, stats=None, want_labels=True, stream=None):
+    """[B,H,W,C] u8 or fp16 class scores (device) -> (labels [B,H,W] u8 | None, stats [B,C,4] int64).
+
+    labels = first index of the per-pixel maximum (the ArgMax the tflite graph ends with,
+    sem_seg_server.py:162-163); stats[b,c] = (n, sum x, sum y, sum winning logit) over the crop
+    [:roi_h,:roi_w] of sem_seg_server.py:164-167.  The stats tensor is int64 holding the library's u64
+    bit patterns (torch has no uint64 arithmetic); view as numpy uint64 on the host."""
+    _require_cuda(logits, "logits")
+    if logits.dim() != 4 or logits.dtype not in (torch.uint8, torch.float16):
+        raise ValueError("logits must be [B,H,W,C] uint8 or float16")
+    b, h, w, c = logits.shape
+    roi_h = h if roi_h is None else roi_h
+    roi_w = w if roi_w is None else roi_w
+    dev = logits.device
+    if want_labels and labels is None:
+        labels = torch.empty((b, h, w), dtype=torch.uint8, device=dev)
+    if stats is None:
+        stats = torch.empty((b, c, 4), dtype=torch.int64, device=dev)
+    _require_cuda(stats, "stats")
+    fn = _cabi.lib.ssb_argmax_stats_u8 if logits.dtype == torch.uint8 else _cabi.lib.ssb_argmax_stats_f16
+    with torch.cuda.device(dev):
+        _cabi.check(fn(logits.data_ptr(), b, h, w, c, roi_h, roi_w,
+                       labels.data_ptr() if want_labels else None, stats.data_ptr(), _stream_ptr(stream)))
+    return (labels if want_labels else None), stats
+
+
+def foreground_mask(labels, roi_h, roi_w, colormap_dev=None, out=None, stream=None):
+    """[B,H,W] u8 label maps (device) -> [B,H,W] u8 mask, 255 where the reference's
+    blur/gray/threshold stage (sem_seg_server.py:173,79-85) is foreground inside the ROI."""
+    _require_cuda(labels, "labels")
+    b, h, w = labels.shape
+    if colormap_dev is None:
+        colormap_dev = torch.from_numpy(create_pascal_label_colormap().astype(np.uint8)).to(labels.device)
+    if out is None:
+        out = torch.empty_like(labels)
+    with torch.cuda.device(labels.device):
+        _cabi.check(_cabi.lib.ssb_fg_mask_u8(labels.data_ptr(), b, h, w, roi_h, roi_w, colormap_dev.data_ptr(),
+                                             out.data_ptr(), _stream_ptr(stream)))
+    return out
+
+
+# ---- host finalisation (floats from exact integers; sem_seg_server.py:111,121-122,187-190) ----------
+def objects_from_stats(stats_frame, width, height, labels, min_area_ratio, scale=1.0, zero_point=0,
+                       fixed_shift=0, only_foreground=True):
+    """One frame's [C,4] integer block -> list of SegmentContour, in the order the reference's
+    producer would push them (one per label, ascending label index).
+
+    area = n (pixels); centroid = (int(sx/n), int(sy/n)) as :121-122; dropped when n is below
+    min_area_ratio*H*W (:94,:141) or, with only_foreground, when the label's colour would not survive
+    the reference's threshold (:82-85).  score = purity of the label's own pixel set = 1.0 (:111);
+    the dequantised mean winning logit is returned as a second value in `score_conf`."""
+    st = np.asarray(stats_frame).view(np.int64).reshape(-1, 4)
+    min_area = min_area_ratio * height * width
+    fg = foreground_label_set(st.shape[0]) if only_foreground else None
+    out, conf = [], []
+    for lab in range(st.shape[0]):
+        n, sx, sy, sq = (int(v) for v in st[lab])
+        if n == 0 or n < min_area or (fg is not None and lab not in fg):
+            continue
+        out.append(SegmentContour(label=labels.get(lab, 0), score=1.0, area=float(n),
+                                  centroid=Centroid(cx=int(sx / n), cy=int(sy / n))))
+        conf.append(scale * ((sq / float(1 << fixed_shift)) / n - zero_point))
+    return out, conf
+
+
+def objects_from_contours(mask, segment_img, min_area, labels):
+    """Reference-literal objects of one frame from the GPU-made foreground mask and label map
+    (both already cropped to the ROI, host numpy): cv2.findContours on the mask, then per contour
+    the polygon area, majority label, purity and moment centroid of sem_seg_server.py:92-133."""
+    import cv2
+    contours, _ = cv2.findContours(np.ascontiguousarray(mask), cv2.RETR_TREE, cv2.CHAIN_APPROX_SIMPLE)
+    objs = []
+    for i in range(len(contours)):
+        area = cv2.contourArea(contours[i])
+        if area < min_area:
+            continue
+        filled = np.zeros_like(segment_img)
+        cv2.drawContours(filled, contours, i, color=255, thickness=-1)
+        inside = segment_img[filled == 255]
+        counts = np.bincount(inside)
+        idx = int(np.argmax(counts))
+        score = int(counts[idx]) / len(inside)
+        m = cv2.moments(contours[i])
+        if not m["m00"]:
+            continue
+        objs.append(SegmentContour(label=labels.get(idx, 0), score=score, area=area,
+                                   centroid=Centroid(cx=int(m["m10"] / m["m00"]), cy=int(m["m01"] / m["m00"]))))
+    return objs
+
+
+def normalise(obj, width, height):
+    """(label, score, area, cx, cy) with the reply normalisation of sem_seg_server.py:184-192."""
+    return (obj.label, obj.score, min(1.0, obj.area / (width * height)),
+            min(1.0, obj.centroid.cx / width), min(1.0, obj.centroid.cy / height))
+
+
+# ---- host-buffer pipeline ---------------------------------------------------------------------------
+class HostPipeline:
+    """Owns an ssb_pipeline (device buffers + streams) for logits that live in host memory."""
+
+    def __init__(self, height, width, num_classes, dtype=np.uint8, frames_per_chunk=16, n_slots=3, device=0):
+        import ctypes
+        self.h, self.w, self.c = height, width, num_classes
+        self.dtype = np.dtype(dtype)
+        self.device = device
+        self._p = ctypes.c_void_p()
+        with torch.cuda.device(device):
+            _cabi.check(_cabi.lib.ssb_pipeline_create(ctypes.byref(self._p), height, width, num_classes,
+                                                      self.dtype.itemsize, frames_per_chunk, n_slots))
+
+    def argmax_stats(self, logits_host, roi_h=None, roi_w=None, labels_out=None, stats_out=None,
+                     want_labels=True):
+        """logits_host: numpy [B,H,W,C] (C-contiguous; pinned memory is fastest) -> (labels|None, stats u64)."""
+        a = logits_host
+        if not (isinstance(a, np.ndarray) and a.flags.c_contiguous and a.dtype == self.dtype
+                and a.shape[1:] == (self.h, self.w, self.c)):
+            raise ValueError("logits_host must be a C-contiguous [B,%d,%d,%d] %s array"
+                             % (self.h, self.w, self.c, self.dtype))
+        b = a.shape[0]
+        if want_labels and labels_out is None:
+            labels_out = np.empty((b, self.h, self.w), np.uint8)
+        if stats_out is None:
+            stats_out = np.empty((b, self.c, 4), np.uint64)
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib.ssb_pipeline_argmax_stats_host(
+                self._p, a.ctypes.data, b, self.h if roi_h is None else roi_h, self.w if roi_w is None else roi_w,
+                labels_out.ctypes.data if want_labels else None, stats_out.ctypes.data))
+        return (labels_out if want_labels else None), stats_out
+
+    def close(self):
+        if self._p:
+            _cabi.lib.ssb_pipeline_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,362 @@
+"""GPU parity tests: the CUDA path (through the C-ABI in libssb200.so) against the oracle and the
+golden fixtures produced by the reference's own code.  Bit-exact for label maps and integer
+statistics; floats derived from them within 1e-6 relative (BASELINE.json north_star)."""
+import ctypes
+import hashlib
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+from oracle import cport, segpath as sp  # noqa: E402  (checker only)
+
+REL_TOL = 1e-6   # north_star: scores and normalised centroids within 1e-6 relative
+
+
+@pytest.fixture(scope="module")
+def ssb():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    return ssb200
+
+
+def digest(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+
+
+def run_gpu(ssb, logits_np, roi_h=None, roi_w=None, want_labels=True):
+    lg = torch.from_numpy(logits_np).cuda()
+    labels, stats = ssb.argmax_stats(lg, roi_h, roi_w, want_labels=want_labels)
+    torch.cuda.synchronize()
+    return (labels.cpu().numpy() if want_labels else None), stats.cpu().numpy().view(np.uint64)
+
+
+def check_vs_oracle(ssb, logits_np, roi_h=None, roi_w=None):
+    labels, stats = run_gpu(ssb, logits_np, roi_h, roi_w)
+    o_labels, o_stats = cport.argmax_stats(logits_np, roi_h, roi_w, threads=8)
+    assert (labels == o_labels).all(), "label map differs at %d pixels" % int((labels != o_labels).sum())
+    assert (stats == o_stats).all(), "stats differ:\n%s\n%s" % (stats[stats != o_stats][:8], o_stats[stats != o_stats][:8])
+    return labels, stats
+
+
+# ---- K2 + K3, u8 --------------------------------------------------------------------------------
+def test_kat1_u8(ssb):
+    q = np.random.default_rng(0).integers(0, 256, (1, 513, 513, 21), dtype=np.uint8)
+    labels, stats = check_vs_oracle(ssb, q)
+    assert digest(labels[0]) == "06ccd4046908a08f"
+    assert stats[0, 0].tolist() == [13026, 3345589, 3334508, 3175759]
+    assert stats[0, 20].tolist() == [12140, 3102486, 3113402, 2958649]
+    n_labels, n_stats = sp.argmax_stats(q)                      # numpy restatement agrees too
+    assert (labels == n_labels).all() and (stats == n_stats).all()
+
+
+@pytest.mark.parametrize("batch", [2, 3, 5, 17])
+def test_u8_batches_straddle_tiles(ssb, batch):
+    """513*513 is odd: frames are misaligned to tiles and quads, the stream has a ragged tail."""
+    q = np.random.default_rng(100 + batch).integers(0, 256, (batch, 513, 513, 21), dtype=np.uint8)
+    check_vs_oracle(ssb, q)
+
+
+@pytest.mark.parametrize("roi", [(1, 1), (513, 1), (1, 513), (288, 513), (384, 513), (513, 384), (200, 300)])
+def test_u8_roi(ssb, roi):
+    q = np.random.default_rng(7).integers(0, 256, (3, 513, 513, 21), dtype=np.uint8)
+    labels, stats = check_vs_oracle(ssb, q, *roi)
+    assert (stats[:, :, 0].sum(axis=1) == roi[0] * roi[1]).all()
+
+
+def test_u8_blobby_long_runs(ssb):
+    q = np.stack([sp.blobby_logits_u8(3 + i, 513, 513, 21) for i in range(4)])
+    check_vs_oracle(ssb, q, 288, 513)
+
+
+def test_u8_adversarial(ssb):
+    h, w, c = 513, 513, 21
+    a0 = np.full((2, h, w, c), 77, np.uint8)                      # every pixel tied -> label 0
+    labels, stats = check_vs_oracle(ssb, a0)
+    assert not labels.any()
+    a1 = np.zeros((2, h, w, c), np.uint8); a1[..., 13] = 255      # one label everywhere
+    check_vs_oracle(ssb, a1)
+    a2 = np.zeros((1, h, w, c), np.uint8)                         # label = x mod C
+    a2[0, :, np.arange(w), np.arange(w) % c] = 200
+    check_vs_oracle(ssb, a2)
+    a3 = np.zeros((1, h, w, c), np.uint8); a3[..., c - 1] = 1     # maximum only in the last channel
+    labels, _ = check_vs_oracle(ssb, a3)
+    assert (labels == c - 1).all()
+    a4 = np.full((1, h, w, c), 255, np.uint8)                     # saturated, all tied
+    check_vs_oracle(ssb, a4)
+
+
+@pytest.mark.parametrize("shape", [(1, 7, 9, 5), (3, 16, 16, 21), (2, 33, 47, 21), (2, 64, 128, 19),
+                                   (1, 1, 2, 21), (1, 3, 1, 21), (4, 40, 24, 2), (1, 300, 301, 19),
+                                   (9, 31, 33, 21), (1, 1024, 2048, 19)])
+def test_u8_shapes(ssb, shape):
+    q = np.random.default_rng(sum(shape)).integers(0, 256, shape, dtype=np.uint8)
+    check_vs_oracle(ssb, q)
+    check_vs_oracle(ssb, q, max(1, shape[1] // 2), max(1, shape[2] - 1))
+
+
+def test_u8_narrow_value_range_many_ties(ssb):
+    q = np.random.default_rng(5).integers(0, 3, (2, 513, 513, 21), dtype=np.uint8)
+    check_vs_oracle(ssb, q)
+
+
+def test_u8_kernel_configs_agree(ssb, monkeypatch):
+    """Every compiled pipeline configuration and the generic kernel give identical bytes."""
+    q = np.random.default_rng(11).integers(0, 256, (5, 513, 513, 21), dtype=np.uint8)
+    want = cport.argmax_stats(q, 288, 513, threads=8)
+    for cfg in ["4,3", "4,4", "4,6", "8,3", "8,4", "generic"]:
+        monkeypatch.setenv("SSB_ARGMAX_CFG", cfg)
+        labels, stats = run_gpu(ssb, q, 288, 513)
+        assert (labels == want[0]).all() and (stats == want[1]).all(), cfg
+    monkeypatch.setenv("SSB_ARGMAX_CFG", "7,7")
+    with pytest.raises(ssb._cabi.SsbError):
+        run_gpu(ssb, q)
+
+
+def test_u8_misaligned_views_take_generic_path(ssb):
+    """A view starting at frame 1 is not 16-byte aligned (frame = 5 526 549 B): same results."""
+    q = np.random.default_rng(12).integers(0, 256, (3, 513, 513, 21), dtype=np.uint8)
+    big = torch.from_numpy(q).cuda()
+    view = big[1:]
+    assert view.data_ptr() % 16 != 0
+    labels, stats = ssb.argmax_stats(view)
+    want = cport.argmax_stats(q[1:], threads=4)
+    assert (labels.cpu().numpy() == want[0]).all()
+    assert (stats.cpu().numpy().view(np.uint64) == want[1]).all()
+
+
+def test_u8_labels_optional_and_stats_rezeroed(ssb):
+    q = np.random.default_rng(13).integers(0, 256, (2, 513, 513, 21), dtype=np.uint8)
+    lg = torch.from_numpy(q).cuda()
+    stats = torch.full((2, 21, 4), 0x5555555555555555, dtype=torch.int64, device="cuda")   # garbage in
+    _, s1 = ssb.argmax_stats(lg, stats=stats, want_labels=False)
+    _, s2 = ssb.argmax_stats(lg, stats=stats, want_labels=False)        # second call: no accumulation
+    want = cport.argmax_stats(q, threads=4, want_labels=False)[1]
+    assert (s2.cpu().numpy().view(np.uint64) == want).all()
+
+
+def test_u8_non_default_stream(ssb):
+    q = np.random.default_rng(14).integers(0, 256, (2, 513, 513, 21), dtype=np.uint8)
+    want = cport.argmax_stats(q, threads=4)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        lg = torch.from_numpy(q).cuda()
+        labels, stats = ssb.argmax_stats(lg, stream=s)
+    s.synchronize()
+    assert (labels.cpu().numpy() == want[0]).all() and (stats.cpu().numpy().view(np.uint64) == want[1]).all()
+
+
+def test_u8_config2_full_size_properties(ssb):
+    """BASELINE config 2 (batch 64 of 513x513x21): size-independent invariants on every frame,
+    full oracle comparison on a few frames."""
+    b, h, w, c = 64, 513, 513, 21
+    g = torch.Generator(device="cuda"); g.manual_seed(1234)
+    lg = torch.randint(0, 256, (b, h, w, c), dtype=torch.uint8, device="cuda", generator=g)
+    roi_h, roi_w = 288, 513
+    labels, stats = ssb.argmax_stats(lg, roi_h, roi_w)
+    st = stats.cpu().numpy().view(np.uint64).astype(np.int64)
+    assert (st[:, :, 0].sum(1) == roi_h * roi_w).all()                             # every ROI pixel once
+    assert (st[:, :, 1].sum(1) == roi_h * (roi_w * (roi_w - 1) // 2)).all()        # sum of all x
+    assert (st[:, :, 2].sum(1) == roi_w * (roi_h * (roi_h - 1) // 2)).all()        # sum of all y
+    mx = lg.amax(dim=-1)                                                            # torch as a 2nd witness
+    assert (st[:, :, 3].sum(1) == mx[:, :roi_h, :roi_w].sum(dim=(1, 2), dtype=torch.int64).cpu().numpy()).all()
+    win = torch.gather(lg, 3, labels.long().unsqueeze(-1)).squeeze(-1)
+    assert bool((win == mx).all())                                                  # label points at a maximum
+    first = (lg == mx.unsqueeze(-1)).to(torch.uint8).argmax(dim=-1)
+    assert bool((first == labels.long()).all())                                     # ... the FIRST one
+    for f in (0, 31, 63):
+        want = cport.argmax_stats(lg[f:f + 1].cpu().numpy(), roi_h, roi_w, threads=4)
+        assert (labels[f].cpu().numpy() == want[0][0]).all() and (st[f].view(np.uint64) == want[1][0]).all()
+
+
+def test_u8_hypothesis_shapes(ssb):
+    from hypothesis import given, settings, strategies as st_
+
+    @settings(max_examples=40, deadline=None)
+    @given(b=st_.integers(1, 4), h=st_.integers(1, 70), w=st_.integers(1, 70), c=st_.sampled_from([2, 3, 19, 21, 32]),
+           seed=st_.integers(0, 2 ** 31), lowrange=st_.booleans(), data=st_.data())
+    def prop(b, h, w, c, seed, lowrange, data):
+        roi_h = data.draw(st_.integers(1, h)); roi_w = data.draw(st_.integers(1, w))
+        q = np.random.default_rng(seed).integers(0, 4 if lowrange else 256, (b, h, w, c), dtype=np.uint8)
+        check_vs_oracle(ssb, q, roi_h, roi_w)
+    prop()
+
+
+def test_u8_hypothesis_voc_width(ssb):
+    """Fast path (C=21/19, wide frames) with random batch / height / ROI / value range."""
+    from hypothesis import given, settings, strategies as st_
+
+    @settings(max_examples=15, deadline=None)
+    @given(b=st_.integers(1, 6), h=st_.integers(20, 200), w=st_.sampled_from([513, 512, 257, 640]),
+           c=st_.sampled_from([19, 21]), seed=st_.integers(0, 2 ** 31), data=st_.data())
+    def prop(b, h, w, c, seed, data):
+        roi_h = data.draw(st_.integers(1, h)); roi_w = data.draw(st_.sampled_from([w, w, max(1, w // 2)]))
+        q = np.random.default_rng(seed).integers(0, 256, (b, h, w, c), dtype=np.uint8)
+        check_vs_oracle(ssb, q, roi_h, roi_w)
+    prop()
+
+
+# ---- fp16 -------------------------------------------------------------------------------------------
+def test_kat3_f16(ssb):
+    h = np.random.default_rng(2).standard_normal((1, 1024, 2048, 19), dtype=np.float32).astype(np.float16)
+    labels, stats = check_vs_oracle(ssb, h)
+    assert digest(labels[0]) == "7e7612187b8000af"
+    assert int(stats[0, 0, 0]) == 109977 and int(stats[0, 18, 0]) == 110044
+
+
+def test_f16_special_values(ssb):
+    rng = np.random.default_rng(7)
+    h = rng.standard_normal((2, 40, 50, 19), dtype=np.float32).astype(np.float16)
+    u = h.view(np.uint16)
+    u[0, 0, 0, :] = [0x8000, 0x0000] + [0xfc00] * 17          # -0 vs +0 tie -> first index
+    u[0, 0, 1, :] = [0x0001, 0x0002, 0x8001] + [0x8400] * 16  # subnormals
+    u[0, 1, :, :5] = rng.integers(0, 0x400, (50, 5))
+    h[1, 2] *= np.float16(1e-3)
+    h[1, 3] *= np.float16(1000)
+    labels, stats = check_vs_oracle(ssb, h, 33, 44)
+    n_labels, n_stats = sp.argmax_stats(h, 33, 44)
+    assert (labels == n_labels).all() and (stats == n_stats).all()
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 128, 19), (1, 33, 47, 21), (3, 17, 5, 4)])
+def test_f16_shapes(ssb, shape):
+    h = (np.random.default_rng(sum(shape)).standard_normal(shape, dtype=np.float32) * 8).astype(np.float16)
+    check_vs_oracle(ssb, h)
+    check_vs_oracle(ssb, h, max(1, shape[1] // 3), max(1, shape[2] // 2))
+
+
+# ---- K1 pre-process ---------------------------------------------------------------------------------
+def gpu_preprocess(ssb, frames_np, W, H, keep=True):
+    b, ch, cw, _ = frames_np.shape
+    geom = ssb.FrameGeometry(cw, ch, W, H, keep)
+    out = ssb.preprocess_frames(torch.from_numpy(frames_np).cuda(), geom)
+    torch.cuda.synchronize()
+    return out.cpu().numpy(), geom
+
+
+def test_preprocess_matches_reference_fixtures(ssb, golden):
+    g = golden("preprocess.npz")
+    for name in sorted(k[:-5] for k in g.files if k.endswith("_geom")):
+        cw, ch, W, H, seed, keep = (int(v) for v in g[name + "_geom"])
+        frame = np.random.default_rng(seed).integers(0, 256, (ch, cw, 3), dtype=np.uint8)
+        out, geom = gpu_preprocess(ssb, frame[None], W, H, bool(keep))
+        assert digest(out[0]) == str(g[name + "_digest"]), name
+        if name + "_out" in g.files:
+            assert (out[0] == g[name + "_out"]).all(), name
+
+
+def test_preprocess_kat2_and_batch(ssb):
+    frames = np.random.default_rng(1).integers(0, 256, (1, 1080, 1920, 3), dtype=np.uint8)
+    out, geom = gpu_preprocess(ssb, frames, 513, 513)
+    assert digest(out[0]) == "b8c5ed5577aafd67"
+    assert (geom.roi_h, geom.roi_w) == (288, 513) and not out[0, 288:].any()
+    more = np.random.default_rng(21).integers(0, 256, (5, 480, 640, 3), dtype=np.uint8)
+    out, geom = gpu_preprocess(ssb, more, 513, 513)
+    for i in range(5):
+        assert (out[i] == sp.preprocess_frame(more[i], 513, 513)[0]).all()
+
+
+@pytest.mark.parametrize("cam", [(101, 37), (37, 101), (5, 5), (641, 479), (1, 9), (1000, 3)])
+def test_preprocess_ragged_sizes(ssb, cam):
+    """Row lengths that are not multiples of 16 bytes: head/tail byte paths on both sides."""
+    cw, ch = cam
+    frames = np.random.default_rng(cw * 7 + ch).integers(0, 256, (3, ch, cw, 3), dtype=np.uint8)
+    for (W, H) in [(33, 33), (40, 24), (513, 513)]:
+        try:
+            want = [sp.preprocess_frame(f, W, H)[0] for f in frames]
+        except ValueError:
+            with pytest.raises(ValueError):
+                ssb.FrameGeometry(cw, ch, W, H)
+            continue
+        out, _ = gpu_preprocess(ssb, frames, W, H)
+        assert (out == np.stack(want)).all()
+    out, _ = gpu_preprocess(ssb, frames, 33, 33, keep=False)                     # stretch branch
+    assert (out == np.stack([sp.preprocess_frame(f, 33, 33, False)[0] for f in frames])).all()
+
+
+# ---- foreground mask + reference-literal objects (f1) --------------------------------------------------
+def test_fg_mask_matches_reference_fixtures(ssb, golden):
+    g = golden("objects.npz")
+    for name in sorted(k[:-10] for k in g.files if k.endswith("_label_map")):
+        lm, fm = g[name + "_label_map"], g[name + "_fgmask"]
+        roi_h, roi_w = fm.shape
+        mask = ssb.foreground_mask(torch.from_numpy(lm[None]).cuda(), roi_h, roi_w).cpu().numpy()[0]
+        assert (mask[:roi_h, :roi_w] == fm).all(), name
+        assert not mask[roi_h:].any() and not mask[:, roi_w:].any()
+
+
+def test_reference_literal_objects_from_gpu_mask(ssb, golden):
+    """sem_seg_server.py:173-195 reproduced from GPU products: label map (K2) -> mask (GPU) ->
+    contours/moments (cv2 on host) -> normalised reply values; bit-exact in FP32."""
+    g = golden("objects.npz")
+    lab = golden("labels_colormap.npz")
+    names = dict(zip(lab["label_ids"].tolist(), lab["label_names"].tolist()))
+    for name in sorted(k[:-5] for k in g.files if k.endswith("_geom")):
+        cw, ch, W, H = (int(v) for v in g[name + "_geom"][:4])
+        geom = ssb.FrameGeometry(cw, ch, W, H)
+        lm = g[name + "_label_map"]
+        # logits whose argmax is the fixture's label map
+        q = np.random.default_rng(1).integers(0, 100, (1, H, W, 21), dtype=np.uint8)
+        np.put_along_axis(q[0], lm[..., None].astype(np.int64), 200, -1)
+        labels, _ = ssb.argmax_stats(torch.from_numpy(q).cuda(), geom.roi_h, geom.roi_w)
+        assert (labels.cpu().numpy()[0] == lm).all()
+        mask = ssb.foreground_mask(labels, geom.roi_h, geom.roi_w).cpu().numpy()[0]
+        seg = labels.cpu().numpy()[0][:geom.roi_h, :geom.roi_w]
+        objs = ssb.objects_from_contours(mask[:geom.roi_h, :geom.roi_w], seg,
+                                         float(g[name + "_min_area_ratio"]) * H * W, names)
+        got = [ssb.normalise(o, W, H) for o in objs][::-1]                         # deque is newest-first
+        assert [o[0] for o in got] == g[name + "_obj_names"].tolist(), name
+        vals = np.array([o[1:] for o in got], dtype=np.float32).reshape(-1, 4)
+        assert (vals == g[name + "_obj_vals"]).all(), name
+
+
+def test_per_label_objects_floats(ssb):
+    """Scores / normalised centroids from GPU integers vs the oracle's floats (1e-6 relative)."""
+    q = np.stack([sp.blobby_logits_u8(30 + i, 513, 513, 21, cell=64, bg_frac=0.5) for i in range(2)])
+    _, stats = run_gpu(ssb, q, 288, 513)
+    names = {i: "l%d" % i for i in range(21)}
+    for f in range(2):
+        objs, conf = ssb.objects_from_stats(stats[f], 513, 513, names, 0.01, scale=0.1, zero_point=128,
+                                            only_foreground=False)
+        want = sp.per_label_objects(cport.argmax_stats(q[f:f + 1], 288, 513)[1][0], 513, 513, names, 0.01,
+                                    scale=0.1, zero_point=128, only_foreground=False)[::-1]
+        assert len(objs) == len(want) and len(objs) >= 2
+        for o, cf, w in zip(objs, conf, want):
+            got = ssb.normalise(o, 513, 513)
+            for a, b in zip(got[1:] + (cf,), (w["score"], w["area"], w["cx"], w["cy"], w["score_conf"])):
+                assert abs(a - b) <= REL_TOL * max(abs(b), 1e-30)
+
+
+# ---- host-buffer pipeline (C-ABI with HOST pointers) ---------------------------------------------------
+def test_host_pipeline_matches_device_path(ssb):
+    q = np.random.default_rng(40).integers(0, 256, (11, 513, 513, 21), dtype=np.uint8)
+    want = cport.argmax_stats(q, 288, 513, threads=8)
+    pipe = ssb.HostPipeline(513, 513, 21, np.uint8, frames_per_chunk=4, n_slots=2)
+    labels, stats = pipe.argmax_stats(q, 288, 513)
+    assert (labels == want[0]).all() and (stats == want[1]).all()
+    _, stats2 = pipe.argmax_stats(q[:3], want_labels=False)                       # reuse, other ROI
+    assert (stats2 == cport.argmax_stats(q[:3], threads=4)[1]).all()
+    pipe.close()
+    h = np.random.default_rng(41).standard_normal((3, 64, 128, 19), dtype=np.float32).astype(np.float16)
+    pipe = ssb.HostPipeline(64, 128, 19, np.float16, frames_per_chunk=2, n_slots=2)
+    labels, stats = pipe.argmax_stats(h)
+    want = cport.argmax_stats(h)
+    assert (labels == want[0]).all() and (stats == want[1]).all()
+
+
+def test_raw_cabi_call_with_ctypes(ssb):
+    """The call a non-torch host would make: raw device pointers from cudaMalloc via the runtime."""
+    q = np.random.default_rng(42).integers(0, 256, (2, 65, 65, 21), dtype=np.uint8)
+    lg = torch.from_numpy(q).cuda()
+    labels = torch.empty((2, 65, 65), dtype=torch.uint8, device="cuda")
+    stats = torch.empty((2, 21, 4), dtype=torch.int64, device="cuda")
+    rc = ssb._cabi.lib.ssb_argmax_stats_u8(ctypes.c_void_p(lg.data_ptr()), 2, 65, 65, 21, 65, 65,
+                                           ctypes.c_void_p(labels.data_ptr()), ctypes.c_void_p(stats.data_ptr()),
+                                           ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    want = cport.argmax_stats(q)
+    assert (labels.cpu().numpy() == want[0]).all() and (stats.cpu().numpy().view(np.uint64) == want[1]).all()
