@@ -180,7 +180,7 @@ def run_ssb(args):
     ev1.record(stream)
     barrier()
     dev_ms = ev0.elapsed_time(ev1)
-    if sampler and dev_ms < 1500:          # keep the GPU under the same load long enough for nvidia-smi to see it
+    if sampler and dev_ms < 1500 and not args.profile:          # keep the GPU under the same load long enough for nvidia-smi to see it
         t_end = time.time() + 1.5
         i = 0
         while time.time() < t_end:
@@ -200,6 +200,13 @@ def run_ssb(args):
               (stats[:2].cpu().numpy().view(np.uint64) == want_s).all())
     if not ok:
         raise SystemExit("bench: GPU result differs from the oracle")
+
+    if args.profile:                       # short run for ncu: device-timed region only
+        if rank == 0:
+            print(json.dumps({"profile_run": True, "ms_per_step": dev_ms / args.steps, "steps": args.steps}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # ---- end to end through the C-ABI with HOST buffers (pinned), H2D + D2H inside the timed region --
     pinned = [torch.from_numpy(b).pin_memory() for b in host_batches[:2]]
@@ -279,6 +286,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ssb", choices=["ssb", "reference"])
+    ap.add_argument("--profile", action="store_true",
+                    help="device-timed region only (no clock hold, e2e or CPU baseline): the command run under ncu")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
