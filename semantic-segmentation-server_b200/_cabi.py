@@ -5,7 +5,7 @@ import ctypes
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "lib", "libssb200.so")
+LIB_PATH = os.environ.get("SSB200_LIB") or os.path.join(_PKG, "lib", "libssb200.so")  # override: A/B tuning only
 
 SSB_OK = 0
 SSB_ERR_BAD_SHAPE, SSB_ERR_BAD_POINTER, SSB_ERR_LIMIT, SSB_ERR_CUDA = -1, -2, -3, -4

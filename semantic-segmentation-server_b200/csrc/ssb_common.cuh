@@ -38,6 +38,18 @@ struct DeviceInfo {
 // Cached per device (the only global state the library keeps); SSB_ERR_CUDA if no device.
 int device_info(DeviceInfo *out);
 
+// ---- scratch workspaces ------------------------------------------------------------------------
+// Device scratch that is ZERO AT REST (kernels leave it zeroed).  A small per-device pool, grown on
+// demand with cudaMalloc (first use, or a larger request than seen before: do that outside stream
+// capture).  A slot that was last used on another stream is ordered behind that use with an event,
+// so concurrent streams never share live scratch.
+struct WorkspaceLease {
+    void *ptr;
+    int dev, slot;
+};
+int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out);
+int workspace_release(const WorkspaceLease &lease, cudaStream_t stream);
+
 // ---- device-side PTX wrappers ----------------------------------------------------------------
 #ifdef __CUDACC__
 __device__ __forceinline__ uint32_t smem_addr(const void *p) {
