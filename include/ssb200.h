@@ -9,8 +9,10 @@
  *
  * Conventions
  *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
- *   - the caller owns every buffer; the library allocates nothing persistent in the device-pointer
- *     entry points and zeroes `stats` itself on the given stream;
+ *   - the caller owns every input/output buffer and `stats` needs no initialisation.  The only device
+ *     memory the library owns is a small zero-at-rest scratch pool per device (a few hundred KB,
+ *     cudaMalloc'ed on first use or when a larger batch than ever before arrives -- warm it up
+ *     outside stream capture) and the ssb_pipeline objects the caller creates explicitly;
  *   - all work is enqueued on `stream` (a cudaStream_t passed as void*, 0 = legacy default stream)
  *     of the CURRENT device; calls are asynchronous with respect to the host and never
  *     synchronise the device; re-entrant across (device, stream) pairs;
