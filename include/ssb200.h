@@ -101,6 +101,32 @@ SSB_API int ssb_argmax_stats_u8(const uint8_t *logits, int B, int H, int W, int 
 SSB_API int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
                          uint8_t *labels, uint64_t *stats, void *stream);
 
+/* No counterpart in the reference: an extra way to call the u8 argmax + statistics pass for hosts
+ * that must not trigger a device allocation.
+ *
+ * ssb_argmax_stats_u8 borrows a small scratch block from a pool that the library grows with
+ * cudaMalloc when it first sees a device (or a bigger batch than before).  Some hosts of this code
+ * cannot tolerate that: a serving process that has already given all of HBM to its own allocator
+ * (the PyTorch caching allocator, RMM, a fixed MPS/MIG memory budget) can see a raw cudaMalloc fail
+ * or fragment its pool, and a frame loop with a latency target cannot afford cudaMalloc's
+ * device-wide synchronisation stalling its other streams in the middle of a run.  For them this
+ * entry point keeps the scratch in an array that is part of the library image itself: it calls no
+ * cudaMalloc, cudaFree or other allocating routine, ever.
+ *
+ * Same arguments, results and limits as ssb_argmax_stats_u8, plus:
+ *   - at most SSB_NOALLOC_MAX_FRAMES frames per call (more is refused with SSB_ERR_LIMIT -- split
+ *     the batch); the array is sized for that many frames of 21 classes, about 173 KB, and every GPU
+ *     that loads the library carries it until the process exits;
+ *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress with
+ *     that device current) and remembers it; make that first call before starting any stream
+ *     capture;
+ *   - all calls on a device share the one array.  Each call clears the part it uses first, so a
+ *     call that was cut short cannot poison the next one, but two calls whose kernels overlap on
+ *     the GPU (different streams, no ordering between them) race on it: order them yourself. */
+#define SSB_NOALLOC_MAX_FRAMES 256
+SSB_API int ssb_argmax_stats_u8_noalloc(const uint8_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
+                                        uint8_t *labels, uint64_t *stats, void *stream);
+
 /* Replaces sem_seg_server.py:173 (label_to_color_image) + :79-85 (blur 3x3, BGR2GRAY, threshold
  * 127) -- the foreground mask handed to cv2.findContours -- with the exact integer formula.
  *

@@ -22,6 +22,8 @@ SIGNATURES = {
                                            _c_int, _c_int, _c_void_p, _c_int, _c_int, _c_void_p]),
     "ssb_argmax_stats_u8": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
                                      _c_void_p, _c_void_p, _c_void_p]),
+    "ssb_argmax_stats_u8_noalloc": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
+                                             _c_void_p, _c_void_p, _c_void_p]),
     "ssb_argmax_stats_f16": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
                                       _c_void_p, _c_void_p, _c_void_p]),
     "ssb_fg_mask_u8": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p,

@@ -416,6 +416,7 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_u8_kernel(cons
 // ---- host side ------------------------------------------------------------------------------------
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "argmax_generic.cuh"
 
@@ -517,4 +518,82 @@ extern "C" int ssb_argmax_stats_u8(const uint8_t *logits, int B, int H, int W, i
     const int rc = C == 21 ? dispatch_cfg<21>(p, st, nw, stg) : dispatch_cfg<19>(p, st, nw, stg);
     const int rc2 = workspace_release(ws, st);
     return rc ? rc : rc2;
+}
+
+// ---- entry point that never allocates ------------------------------------------------------------
+// Same computation as ssb_argmax_stats_u8, but the streaming kernel's scratch (the zero-at-rest
+// [B][C][4] accumulators and [B] pixel counters) lives in a fixed array inside the loaded module
+// instead of coming from the cudaMalloc-backed workspace pool.  See include/ssb200.h for who needs
+// this and what it costs.
+namespace ssb {
+namespace {
+
+constexpr int kNoAllocMaxFrames = SSB_NOALLOC_MAX_FRAMES;
+constexpr int kNoAllocMaxClasses = 21;  // the classes the streaming kernel is compiled for: 19 and 21
+constexpr size_t kNoAllocAccBytes = sizeof(uint64_t) * 4 * kNoAllocMaxClasses * kNoAllocMaxFrames;
+constexpr size_t kNoAllocBytes = kNoAllocAccBytes + sizeof(unsigned int) * kNoAllocMaxFrames;
+
+// Resident on every GPU that loads the library until the process exits (~173 KB).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not something a kernel can
+// dereference: the device address has to be asked for, per device, with that device current.
+int noalloc_scratch_address(unsigned char **out) {
+    static unsigned char *cached[64] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    SSB_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(SSB_ERR_LIMIT, "device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void *ptr = nullptr;
+        SSB_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        cached[dev] = static_cast<unsigned char *>(ptr);
+    }
+    *out = cached[dev];
+    return SSB_OK;
+}
+
+}  // namespace
+}  // namespace ssb
+
+extern "C" int ssb_argmax_stats_u8_noalloc(const uint8_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
+                                           uint8_t *labels, uint64_t *stats, void *stream) {
+    using namespace ssb;
+    if (int rc = check_argmax_args(logits, B, H, W, C, roi_h, roi_w, stats)) return rc;
+    if (B > kNoAllocMaxFrames)
+        return fail(SSB_ERR_LIMIT, "ssb_argmax_stats_u8_noalloc takes at most %d frames per call (got %d); split the batch",
+                    kNoAllocMaxFrames, B);
+    if (B == 0) return SSB_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    auto *stats64 = reinterpret_cast<unsigned long long *>(stats);
+    const int nw = 8, stg = 3;
+    const bool aligned = (reinterpret_cast<uintptr_t>(logits) % 16 == 0) && (reinterpret_cast<uintptr_t>(labels) % 4 == 0);
+    const long long total_px = static_cast<long long>(B) * H * W;
+    if (!(aligned && W >= 4 && (C == 19 || C == 21) && total_px >= 128ll * nw)) {
+        // shapes the streaming kernel does not cover use the generic kernel, which needs no scratch
+        SSB_CUDA_TRY(cudaMemsetAsync(stats64, 0, sizeof(uint64_t) * 4 * C * static_cast<size_t>(B), st));
+        return launch_generic<ElemU8>(logits, B, H, W, C, roi_h, roi_w, labels, stats64, st);
+    }
+    unsigned char *scratch = nullptr;
+    if (int rc = noalloc_scratch_address(&scratch)) return rc;
+    const size_t acc_bytes = sizeof(uint64_t) * 4 * C * static_cast<size_t>(B);
+    const size_t used = acc_bytes + sizeof(unsigned int) * static_cast<size_t>(B);
+    // The array is shared by every call and still holds whatever the previous call left (zeros if
+    // it ran to completion, anything if it was cut short): start from a clean slate.
+    SSB_CUDA_TRY(cudaMemsetAsync(scratch, 0, used, st));
+
+    ArgmaxParams p{};
+    p.logits = logits;
+    p.labels = labels;
+    p.stats = stats64;
+    p.total_px = total_px;
+    p.acc = reinterpret_cast<unsigned long long *>(scratch);
+    p.frame_px = reinterpret_cast<unsigned int *>(scratch + acc_bytes);
+    p.hw = H * W;
+    p.w = W;
+    p.roi_h = roi_h;
+    p.roi_w = roi_w;
+    p.divw = make_fastdiv(static_cast<uint32_t>(W));
+    return C == 21 ? dispatch_cfg<21>(p, st, nw, stg) : dispatch_cfg<19>(p, st, nw, stg);
 }
