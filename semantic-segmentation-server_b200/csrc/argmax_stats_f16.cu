@@ -1,7 +1,163 @@
-// fp16 entry point of the fused argmax + per-label statistics (Cityscapes-shaped config:
-// 1024x2048x19 fp16).  Same contract as the u8 path (ssb200.h); SQ is the exact fixed-point sum
-// value * 2^24 of the winning logits.
-#include "argmax_generic.cuh"
+// fp16 codec + C-ABI entry point of the fused argmax + per-label statistics kernel (Cityscapes-shaped
+// config: 1024x2048x19 fp16).  argmax_stream.cuh has the design notes and the kernel itself.
+//
+// A lane owns 4 consecutive pixels = C aligned 64-bit words of the tile (stride C x 8 bytes between
+// lanes: conflict-free LDS.64 for odd C).  Per pixel: the maximum with HMNMX2 over half2 words (halves
+// that belong to a neighbouring pixel are replaced by -inf), then the FIRST channel equal to it from
+// per-word HSET2 equality masks: floating-point `==`, so -0 and +0 tie and the first index wins, as
+// np.argmax does.  Inputs must be NaN-free.  Σq_max is the exact fixed-point sum of value * 2^24, kept
+// as a second 64-bit word next to the packed n/Σk/Σj/Σdy word (16-byte entries, LDS.128/STS.128).
+#include <cuda_fp16.h>
+
+#include "argmax_stream.cuh"
+
+namespace ssb {
+namespace {
+
+__device__ __forceinline__ uint32_t hmax2_bits(uint32_t a, uint32_t b) {
+    const __half2 r = __hmax2(*reinterpret_cast<const __half2 *>(&a), *reinterpret_cast<const __half2 *>(&b));
+    return *reinterpret_cast<const uint32_t *>(&r);
+}
+__device__ __forceinline__ uint32_t heq2_mask_bits(uint32_t a, uint32_t b) {
+    return __heq2_mask(*reinterpret_cast<const __half2 *>(&a), *reinterpret_cast<const __half2 *>(&b));
+}
+
+template <int C>
+struct CodecF16 {
+    static constexpr int kC = C, kElemBytes = 2, kQuadWords = 2 * C, kEntryBytes = 16;
+    using Elem = ElemF16;
+    struct Ctx {
+        uint32_t ninf2;   // half2(-inf, -inf), kept in a register (see the u8 codec on why via smem)
+    };
+    static __device__ __forceinline__ void store_table(uint32_t *tab) { tab[0] = 0xFC00FC00u; }
+    static __device__ __forceinline__ Ctx load_ctx(const uint32_t *tab) {
+        return Ctx{*reinterpret_cast<const volatile uint32_t *>(tab)};
+    }
+
+    static __device__ __forceinline__ void load_quad(const uint8_t *stage, int quad, uint32_t (&w)[2 * C]) {
+        const uint2 *src = reinterpret_cast<const uint2 *>(stage) + quad * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            const uint2 v = src[c];
+            w[2 * c] = v.x;
+            w[2 * c + 1] = v.y;
+        }
+    }
+
+    // key = (bits of the maximum << 16) | (255 - label)
+    static __device__ __forceinline__ uint32_t pixel_key(const uint32_t (&w)[2 * C], int j, const Ctx &ctx) {
+        const int h0 = j * C, h1 = (j + 1) * C;          // halves [h0, h1) of the quad belong to pixel j
+        const int wd0 = h0 / 2, wd1 = (h1 - 1) / 2;      // words wd0..wd1
+        uint32_t v[C / 2 + 2];
+        int nv = 0;
+#pragma unroll
+        for (int wd = wd0; wd <= wd1; ++wd) {
+            const bool lo = 2 * wd >= h0, hi = 2 * wd + 1 < h1;
+            // foreign halves -> -inf: PRMT picks bytes 0-3 from the word, 4-7 from half2(-inf,-inf)
+            v[nv++] = lo && hi ? w[wd] : __byte_perm(w[wd], ctx.ninf2, lo ? 0x5410u : 0x3254u);
+        }
+        uint32_t m2 = v[0];
+#pragma unroll
+        for (int i = 1; i < nv; ++i) m2 = hmax2_bits(m2, v[i]);
+        m2 = hmax2_bits(m2, __byte_perm(m2, 0u, 0x1032u));   // both halves = the pixel's maximum
+        // equality mask: bit i (low halves) / bit 16+i (high halves) for word wd0+i
+        uint32_t acc = 0;
+#pragma unroll
+        for (int i = 0; i < nv; ++i) {
+            const int wd = wd0 + i;
+            const bool lo = 2 * wd >= h0, hi = 2 * wd + 1 < h1;
+            const uint32_t bits = (lo ? 1u << i : 0u) | (hi ? 1u << (16 + i) : 0u);
+            acc |= heq2_mask_bits(v[i], m2) & bits;
+        }
+        // low half of word wd0+i is channel 2*(wd0+i) - h0, high half is that + 1
+        const int off = 2 * wd0 - h0;                     // 0 or -1
+        const uint32_t lo16 = acc & 0xffffu, hi16 = acc >> 16;
+        const uint32_t cl = lo16 ? 2u * (__ffs(lo16) - 1) + off : 255u;
+        const uint32_t ch = hi16 ? 2u * (__ffs(hi16) - 1) + off + 1 : 255u;
+        const uint32_t label = min(cl, ch);
+        return (m2 << 16) | (255u - label);
+    }
+
+    static __device__ __forceinline__ void classify(const uint32_t (&w)[2 * C], const Ctx &ctx, uint32_t (&key)[4]) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) key[j] = pixel_key(w, j, ctx);
+    }
+
+    // Four 128-bit read-modify-writes: [packed n|Σk|Σj|Σdy : u64][Σ value*2^24 : i64]; loads first,
+    // addends forwarded between equal labels (see the u8 codec).
+    static __device__ __forceinline__ void add4(uint32_t hist_lane, const uint32_t (&key)[4], uint32_t lo_base,
+                                                const uint32_t (&add_hi)[4], const bool (&counted)[4]) {
+        uint32_t addr[4];
+        unsigned long long a[4], q[4], ea[4], eq[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            addr[j] = hist_lane - (key[j] & 0xffu) * (32u * kEntryBytes);
+            a[j] = counted[j] ? ((static_cast<unsigned long long>(add_hi[j]) << 32) | lo_base) : 0ull;
+            q[j] = counted[j] ? static_cast<unsigned long long>(half_bits_to_fixed24(key[j] >> 16)) : 0ull;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t x0, x1, x2, x3;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(addr[j]));
+            ea[j] = (static_cast<unsigned long long>(x1) << 32) | x0;
+            eq[j] = (static_cast<unsigned long long>(x3) << 32) | x2;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            unsigned long long va = ea[j] + a[j], vq = eq[j] + q[j];
+#pragma unroll
+            for (int i = 0; i < j; ++i) {
+                const bool same = addr[i] == addr[j];
+                va += same ? a[i] : 0ull;
+                vq += same ? q[i] : 0ull;
+            }
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr[j]), "r"(static_cast<uint32_t>(va)),
+                         "r"(static_cast<uint32_t>(va >> 32)), "r"(static_cast<uint32_t>(vq)),
+                         "r"(static_cast<uint32_t>(vq >> 32)));
+        }
+    }
+
+    static __device__ __forceinline__ RowTotals row_totals(const uint8_t *hist, int l, int lane) {
+        const ulonglong2 *row = reinterpret_cast<const ulonglong2 *>(hist) + l * 32;
+        unsigned long long nk = 0, sq = 0;
+        uint32_t sj = 0, sdy = 0, cw = 0;
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) {
+            const int c = (lane + i) & 31;
+            const ulonglong2 e = row[c];
+            nk += e.x & 0x0000003FFF0000FFull;        // n at 0 (headroom to 24), Σk at 24 (headroom to 64)
+            sj += static_cast<uint32_t>(e.x >> kFieldJ) & 0x3FFu;
+            sdy += static_cast<uint32_t>(e.x >> kFieldDy);
+            cw += (static_cast<uint32_t>(e.x) & 0xFFu) * c;
+            sq += e.y;                                // two's complement: wraps correctly
+        }
+        RowTotals t;
+        t.n = static_cast<long long>(nk & 0xFFFFFFull);
+        t.sk = static_cast<long long>(nk >> 24);
+        t.sq = static_cast<long long>(sq);
+        t.sj = sj;
+        t.sdy = sdy;
+        t.cw = cw;
+        return t;
+    }
+
+    static __device__ __forceinline__ void clear_column(uint8_t *hist, int lane) {
+        ulonglong2 *h = reinterpret_cast<ulonglong2 *>(hist);
+#pragma unroll
+        for (int l = 0; l < C; ++l) h[l * 32 + lane] = make_ulonglong2(0ull, 0ull);
+    }
+};
+
+template <int C>
+int dispatch_cfg(const ArgmaxParams &p, cudaStream_t st, int nw, int stg) {
+    if (nw == 4 && stg == 3) return launch_stream<CodecF16<C>, 4, 3>(p, st);
+    if (nw == 4 && stg == 4) return launch_stream<CodecF16<C>, 4, 4>(p, st);
+    if (nw == 8 && stg == 2) return launch_stream<CodecF16<C>, 8, 2>(p, st);
+    return fail(SSB_ERR_LIMIT, "no fp16 kernel compiled for NWARPS=%d STAGES=%d", nw, stg);
+}
+
+}  // namespace
+}  // namespace ssb
 
 extern "C" int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
                                     uint8_t *labels, uint64_t *stats, void *stream) {
@@ -10,6 +166,22 @@ extern "C" int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W,
     if (B == 0) return SSB_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     auto *stats64 = reinterpret_cast<unsigned long long *>(stats);
-    SSB_CUDA_TRY(cudaMemsetAsync(stats64, 0, sizeof(uint64_t) * 4 * C * static_cast<size_t>(B), st));
-    return launch_generic<ElemF16>(logits, B, H, W, C, roi_h, roi_w, labels, stats64, st);
+    int nw = 4, stg = 3;
+    bool force_generic = false;
+    if (const char *env = getenv("SSB_ARGMAX_F16_CFG")) {   // tuning knob (benchmarks only)
+        if (!strcmp(env, "generic")) force_generic = true;
+        else if (sscanf(env, "%d,%d", &nw, &stg) != 2) return fail(SSB_ERR_LIMIT, "bad SSB_ARGMAX_F16_CFG '%s'", env);
+    }
+    const long long total_px = static_cast<long long>(B) * H * W;
+    const bool fast = !force_generic && (C == 19 || C == 21) && stream_path_ok(logits, labels, W, total_px, nw);
+    if (!fast) {
+        SSB_CUDA_TRY(cudaMemsetAsync(stats64, 0, sizeof(uint64_t) * 4 * C * static_cast<size_t>(B), st));
+        return launch_generic<ElemF16>(logits, B, H, W, C, roi_h, roi_w, labels, stats64, st);
+    }
+    WorkspaceLease ws;
+    if (int rc = workspace_acquire(scratch_bytes(B, C), st, &ws)) return rc;
+    const ArgmaxParams p = make_params(logits, B, H, W, C, roi_h, roi_w, labels, stats64, ws.ptr);
+    const int rc = C == 21 ? dispatch_cfg<21>(p, st, nw, stg) : dispatch_cfg<19>(p, st, nw, stg);
+    const int rc2 = workspace_release(ws, st);
+    return rc ? rc : rc2;
 }
