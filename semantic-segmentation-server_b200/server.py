@@ -1,0 +1,219 @@
+"""Drop-in for the reference's server module (sem_seg_server.py): same gRPC service, same flags, same
+reply semantics, with the per-frame path running on the GPU in batches.
+
+    recognize_and_segment   sem_seg_server.py:135-213   producer loop (batched)
+    SemanticSegmentationServicer  :216-234              LIFO pop x num_detections, padded with empties
+    serve                   :236-291                    flags, engine/labels/camera set-up, gRPC lifecycle
+
+The model (`engine`) is a duck type, as in the reference: `get_input_tensor_shape()` -> (1,H,W,3) and
+`run_logits(input_u8 [B,H,W,3] cuda) -> (logits [B,H,W,C] cuda u8|f16, scale, zero_point)`.  The Edge
+TPU tflite model is unavailable here; `SyntheticEngine` produces class scores of the model's exact
+output shape and quantisation.
+"""
+import argparse
+import collections
+import concurrent.futures
+import os
+
+import numpy as np
+import torch
+
+from . import hotpath, proto
+
+# Stack (LIFO deque) shared by the producer thread and the RPC handlers (sem_seg_server.py:28).
+segmented_objects = collections.deque()
+
+
+class SyntheticEngine:
+    """Stands in for BasicEngine (sem_seg_server.py:264): quantised class scores derived from the
+    input image so that results are deterministic and depend on the frame."""
+
+    def __init__(self, height=513, width=513, num_classes=21, scale=1.0 / 16, zero_point=128):
+        self.h, self.w, self.c, self.scale, self.zero_point = height, width, num_classes, scale, zero_point
+
+    def get_input_tensor_shape(self):
+        return (1, self.h, self.w, 3)
+
+    def run_logits(self, x):
+        b = x.shape[0]
+        lum = x.to(torch.int32).sum(dim=-1)                                    # [B,H,W]
+        ch = torch.arange(self.c, device=x.device, dtype=torch.int32)
+        q = ((lum.unsqueeze(-1) * (ch * 7 + 3) + ch * 31) % 256).to(torch.uint8)
+        return q.contiguous().view(b, self.h, self.w, self.c), self.scale, self.zero_point
+
+
+class ArrayCamera:
+    """cv2.VideoCapture look-alike over an in-memory list of BGR frames (tests, benchmarks)."""
+
+    def __init__(self, frames):
+        self._frames, self._i = list(frames), 0
+
+    def isOpened(self):
+        return True
+
+    def read(self):
+        if self._i >= len(self._frames):
+            return False, None
+        self._i += 1
+        return True, self._frames[self._i - 1]
+
+    def release(self):
+        pass
+
+    def get(self, prop):
+        import cv2
+        h, w = self._frames[0].shape[:2]
+        return {cv2.CAP_PROP_FRAME_WIDTH: w, cv2.CAP_PROP_FRAME_HEIGHT: h}.get(prop, 0)
+
+
+def _open_camera(camera_idx):
+    if hasattr(camera_idx, "read"):
+        return camera_idx
+    import cv2
+    return cv2.VideoCapture(camera_idx)
+
+
+def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_area_ratio,
+                          batch_frames=16, mode="contours", device=0, max_frames=None):
+    """Recognize and segment objects from camera frames (sem_seg_server.py:135-213), `batch_frames`
+    frames per GPU pass.  `mode`: "contours" reproduces the reference's objects (per contour of the
+    thresholded colour image); "labels" emits the per-label objects of the fused statistics."""
+    segmented_objects.clear()
+    _, height, width, _ = engine.get_input_tensor_shape()
+    segment_centroid_min_area = min_area_ratio * height * width
+    dev = torch.device("cuda", device)
+    cap = _open_camera(camera_idx)
+    geom = None
+    done = 0
+    try:
+        while cap.isOpened():
+            frames = []
+            while len(frames) < batch_frames:
+                ret, frame = cap.read()
+                if not ret:
+                    break
+                frames.append(frame)
+            if not frames:
+                break
+            cam_h, cam_w = frames[0].shape[:2]
+            if geom is None or (geom.cam_w, geom.cam_h) != (cam_w, cam_h):
+                geom = hotpath.FrameGeometry(cam_w, cam_h, width, height, keep_aspect_ratio)
+            batch = torch.from_numpy(np.stack(frames)).to(dev, non_blocking=True)
+            inputs = hotpath.preprocess_frames(batch, geom)                       # :150-161
+            logits, scale, zero_point = engine.run_logits(inputs)                 # :162 (model, upstream)
+            label_maps, stats = hotpath.argmax_stats(logits, geom.roi_h, geom.roi_w)   # :163-170, :102-122
+            if mode == "contours":
+                masks = hotpath.foreground_mask(label_maps, geom.roi_h, geom.roi_w)   # :173, :79-85
+                masks_h = masks[:, :geom.roi_h, :geom.roi_w].cpu().numpy()
+                labels_h = label_maps[:, :geom.roi_h, :geom.roi_w].cpu().numpy()
+            else:
+                stats_h = stats.cpu().numpy()
+            for i in range(len(frames)):
+                if mode == "contours":
+                    objs = hotpath.objects_from_contours(masks_h[i], labels_h[i], segment_centroid_min_area, labels)
+                else:
+                    objs, _ = hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, scale,
+                                                         zero_point, fixed_shift=0 if logits.dtype == torch.uint8
+                                                         else hotpath._cabi.F16_FIXED_SHIFT)
+                for o in objs:
+                    lab, score, area, cx, cy = hotpath.normalise(o, width, height)  # :184-192
+                    segmented_objects.appendleft(proto.SegmentedObject(
+                        label=lab, score=score, area=area, centroid=proto.SegmentedObject.Centroid(cx=cx, cy=cy)))
+            done += len(frames)
+            if max_frames is not None and done >= max_frames:
+                break
+    except KeyboardInterrupt:
+        pass
+    finally:
+        cap.release()
+    return
+
+
+class SemanticSegmentationServicer:
+    """sem_seg_server.py:216-234, registered through generic handlers (no generated grpc module)."""
+
+    def __init__(self, num_detections, camera_res):
+        self.num_detections = num_detections
+        self.camera_res = camera_res
+
+    def GetCameraResolution(self, request, context):
+        return proto.CameraResolution(width=self.camera_res[0], height=self.camera_res[1])
+
+    def GetSegmentedObjects(self, request, context):
+        def pop_deque():
+            try:
+                return segmented_objects.popleft()
+            except IndexError:
+                return proto.SegmentedObject()      # stack empty: empty object (:229-231)
+        return proto.SegmentedObjectData(data=[pop_deque() for _ in range(self.num_detections)])
+
+
+def add_SemanticSegmentationServicer_to_server(servicer, server):
+    """Same registration as sem_seg_server_pb2_grpc.py:48-63."""
+    import grpc
+    handlers = {
+        "GetSegmentedObjects": grpc.unary_unary_rpc_method_handler(
+            servicer.GetSegmentedObjects, request_deserializer=proto.Empty.FromString,
+            response_serializer=proto.SegmentedObjectData.SerializeToString),
+        "GetCameraResolution": grpc.unary_unary_rpc_method_handler(
+            servicer.GetCameraResolution, request_deserializer=proto.Empty.FromString,
+            response_serializer=proto.CameraResolution.SerializeToString),
+    }
+    server.add_generic_rpc_handlers(
+        (grpc.method_handlers_generic_handler("%s.%s" % (proto.PACKAGE, proto.SERVICE), handlers),))
+
+
+class SemanticSegmentationStub:
+    """Client stub equivalent to sem_seg_server_pb2_grpc.py:7-26."""
+
+    def __init__(self, channel):
+        self.GetSegmentedObjects = channel.unary_unary(
+            proto.METHOD_GET_OBJECTS, request_serializer=proto.Empty.SerializeToString,
+            response_deserializer=proto.SegmentedObjectData.FromString)
+        self.GetCameraResolution = channel.unary_unary(
+            proto.METHOD_GET_RESOLUTION, request_serializer=proto.Empty.SerializeToString,
+            response_deserializer=proto.CameraResolution.FromString)
+
+
+def build_arg_parser():
+    default_model_dir = "/media/mendel/sem-seg-server/models"
+    parser = argparse.ArgumentParser()
+    parser.add_argument("--model", help=".tflite model path (unused: synthetic class scores)",
+                        default=os.path.join(default_model_dir, "deeplabv3_mnv2_pascal_quant_edgetpu.tflite"))
+    parser.add_argument("--labels", help="label file path",
+                        default=os.path.join(default_model_dir, "pascal_voc_segmentation_labels.txt"))
+    parser.add_argument("--keep_aspect_ratio", dest="keep_aspect_ratio", action="store_true",
+                        help="keep the image aspect ratio when down-sampling by adding zero padding on bottom or right")
+    parser.add_argument("--camera_idx", type=int, help="Index of which video source to use.", default=1)
+    parser.add_argument("--num_detections", type=int, help="Number of detections to return.", default=3)
+    parser.add_argument("--min_area_ratio", type=float, help="segment centroid min area ratio.", default=0.05)
+    parser.add_argument("--batch_frames", type=int, default=16, help="frames per GPU pass (new)")
+    parser.add_argument("--mode", choices=["contours", "labels"], default="contours", help="object definition (new)")
+    parser.add_argument("--port", default="[::]:50051")
+    parser.set_defaults(keep_aspect_ratio=True)      # as the reference: always true (:246-259)
+    return parser
+
+
+def serve(argv=None):
+    import cv2
+    import grpc
+    args = build_arg_parser().parse_args(argv)
+    print("Loading {} with {} labels.".format(args.model, args.labels))
+    engine = SyntheticEngine()
+    labels = hotpath.load_labels(args.labels)
+    cap = cv2.VideoCapture(args.camera_idx)
+    camera_res = int(cap.get(cv2.CAP_PROP_FRAME_WIDTH)), int(cap.get(cv2.CAP_PROP_FRAME_HEIGHT))
+    cap.release()
+    with concurrent.futures.ThreadPoolExecutor(max_workers=10) as executor:
+        future = executor.submit(recognize_and_segment, args.keep_aspect_ratio, args.camera_idx, engine, labels,
+                                 args.min_area_ratio, args.batch_frames, args.mode)
+        server = grpc.server(executor)
+        add_SemanticSegmentationServicer_to_server(SemanticSegmentationServicer(args.num_detections, camera_res), server)
+        server.add_insecure_port(args.port)
+        server.start()
+        future.result()
+        server.stop(None)
+
+
+if __name__ == "__main__":
+    serve()
