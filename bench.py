@@ -136,6 +136,55 @@ def run_reference(args):
     }))
 
 
+def _time_us(torch, fn, iters):
+    for i in range(3):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters * 1e3
+
+
+def other_kernels(ssb200, torch):
+    """Device-timed figures for the rest of the path (CUDA events, inputs resident and rotated):
+    K1 pre-process at config 3's frame size, the fp16 Cityscapes-shaped argmax+stats of config 5
+    (8 frames per GPU here), and the foreground-mask kernel."""
+    out = []
+    peak, _ = measured_peak()
+    g = torch.Generator(device="cuda"); g.manual_seed(7)
+    b = 64
+    frames = [torch.randint(0, 256, (b, 1080, 1920, 3), dtype=torch.uint8, device="cuda", generator=g) for _ in range(2)]
+    geom = ssb200.FrameGeometry(1920, 1080, H, W)
+    rgb = torch.empty((b, H, W, 3), dtype=torch.uint8, device="cuda")
+    us = _time_us(torch, lambda i: ssb200.preprocess_frames(frames[i % 2], geom, out=rgb), 40)
+    sector = (geom.new_h * 1920 * 3 + H * W * 3) * b
+    out.append({"kernel": "preprocess_nearest (1920x1080 -> 513x513, batch 64)", "us": us, "frames_per_s": b / us * 1e6,
+                "GBps_sampled_plus_output": (geom.new_h * geom.new_w * 3 + H * W * 3) * b / us / 1e3,
+                "GBps_sector_effective": sector / us / 1e3, "frac_of_measured_peak": sector / us / 1e3 / peak})
+    del frames
+    b = 8
+    lg = [torch.randn((b, 1024, 2048, 19), dtype=torch.float16, device="cuda", generator=g) for _ in range(2)]
+    lab = torch.empty((b, 1024, 2048), dtype=torch.uint8, device="cuda")
+    st = torch.empty((b, 19, 4), dtype=torch.int64, device="cuda")
+    us = _time_us(torch, lambda i: ssb200.argmax_stats(lg[i % 2], labels=lab, stats=st), 40)
+    algo = (1024 * 2048 * 19 * 2 + 1024 * 2048 + 19 * 32) * b
+    out.append({"kernel": "argmax_stats fp16 (1024x2048x19, batch 8)", "us": us, "frames_per_s": b / us * 1e6,
+                "GBps": algo / us / 1e3, "frac_of_measured_peak": algo / us / 1e3 / peak})
+    del lg
+    b = 64
+    labels = torch.randint(0, 21, (b, H, W), dtype=torch.uint8, device="cuda", generator=g)
+    mask = torch.empty_like(labels)
+    cm = torch.from_numpy(ssb200.create_pascal_label_colormap().astype(np.uint8)).cuda()
+    us = _time_us(torch, lambda i: ssb200.foreground_mask(labels, ROI_H, ROI_W, cm, out=mask), 20)
+    out.append({"kernel": "fg_mask (513x513, batch 64)", "us": us, "frames_per_s": b / us * 1e6,
+                "GBps": 2 * H * W * b / us / 1e3})
+    return out
+
+
 def run_ssb(args):
     import torch
     import torch.distributed as dist
@@ -228,6 +277,10 @@ def run_ssb(args):
         raise SystemExit("bench: e2e result differs from the oracle")
     pipe.close()
 
+    # ---- the path's other kernels, rank 0, outside every timed region above (informative) -----------
+    other = other_kernels(ssb200, torch) if rank == 0 else None
+    barrier()
+
     # ---- max over ranks ------------------------------------------------------------------------------
     times = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -263,18 +316,19 @@ def run_ssb(args):
                        "sharding": "frames by GPU, no collective"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "argmax_stats_u8_kernel<21,...>",
+                         "kernel": "argmax_stats_stream_kernel<CodecU8<21>,8,3>",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": threads, "kind": "port",
                              "sample": "%d passes over one %d-frame batch in %.1f s, C port, %d threads; "
                                        "numpy restatement 1 thread: %.1f frames/s" % (passes, BATCH, cpu_el, threads,
                                                                                        numpy_fps)},
-            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": BATCH * H * W * C,
-                    "d2h_bytes_per_step": BATCH * (H * W + C * 32), "steps": e2e_steps,
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": world * BATCH * H * W * C,
+                    "d2h_bytes_per_step": world * BATCH * (H * W + C * 32), "steps": e2e_steps,
                     "api": "ssb_pipeline_argmax_stats_host (pinned host buffers, 3 streams x 16-frame chunks)"},
             "gpu_launches": world * args.steps,
             "clocks": clocks,
+            "other_kernels": other,
         }))
     if world > 1:
         dist.destroy_process_group()

@@ -16,34 +16,58 @@ __device__ __forceinline__ int reflect101(int i, int n) {
     return i;
 }
 
+// Each thread produces 4 horizontally adjacent mask pixels: 6 column sums (3 rows each) of packed
+// colours are shared by the 4 box sums, so a pixel costs 4.5 label loads and 4.5 LUT reads instead
+// of 9 + 9.  The colour LUT packs channel 0/1 into 16-bit fields of one word (box sums <= 9*255 fit)
+// and channel 2 into a second word, so a box sum is 2 integer adds per neighbour.
+constexpr int kMaskPxPerThread = 4, kMaskTileW = 32 * kMaskPxPerThread, kMaskTileH = 8;
+
 __global__ void __launch_bounds__(256)
 fg_mask_kernel(const uint8_t *__restrict__ labels, int H, int W, int roi_h, int roi_w,
                const uint8_t *__restrict__ colormap, uint8_t *__restrict__ mask) {
-    __shared__ uint32_t cmap[256];  // packed c0 | c1<<8 | c2<<16
+    __shared__ uint2 cmap[256];  // .x = c0 | c1<<16, .y = c2
     for (int i = threadIdx.x; i < 256; i += blockDim.x)
-        cmap[i] = colormap[3 * i] | (colormap[3 * i + 1] << 8) | (colormap[3 * i + 2] << 16);
+        cmap[i] = make_uint2(colormap[3 * i] | (colormap[3 * i + 1] << 16), colormap[3 * i + 2]);
     __syncthreads();
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
-    const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= W || y >= H) return;
-    const long long fbase = static_cast<long long>(blockIdx.z) * H * W;
-    uint8_t m = 0;
-    if (x < roi_w && y < roi_h) {
-        int s0 = 0, s1 = 0, s2 = 0;
-#pragma unroll
-        for (int dy = -1; dy <= 1; ++dy) {
-            const uint8_t *row = labels + fbase + static_cast<long long>(reflect101(y + dy, roi_h)) * W;
-#pragma unroll
-            for (int dx = -1; dx <= 1; ++dx) {
-                const uint32_t c = cmap[row[reflect101(x + dx, roi_w)]];
-                s0 += c & 0xff; s1 += (c >> 8) & 0xff; s2 += (c >> 16) & 0xff;
-            }
-        }
-        const int b0 = (2 * s0 + 9) / 18, b1 = (2 * s1 + 9) / 18, b2 = (2 * s2 + 9) / 18;
-        const int gray = (b0 * 1868 + b1 * 9617 + b2 * 4899 + 8192) >> 14;
-        m = gray > 127 ? 255 : 0;
+    const int x0 = blockIdx.x * kMaskTileW + (threadIdx.x & 31) * kMaskPxPerThread;
+    const int y = blockIdx.y * kMaskTileH + (threadIdx.x >> 5);
+    if (x0 >= W || y >= H) return;
+    uint8_t *out = mask + static_cast<long long>(blockIdx.z) * H * W + static_cast<long long>(y) * W + x0;
+    const int n_out = min(kMaskPxPerThread, W - x0);
+    if (y >= roi_h || x0 >= roi_w) {
+        for (int j = 0; j < n_out; ++j) out[j] = 0;
+        return;
     }
-    mask[fbase + static_cast<long long>(y) * W + x] = m;
+    const uint8_t *frame = labels + static_cast<long long>(blockIdx.z) * H * W;
+    const uint8_t *rows[3] = {frame + static_cast<long long>(reflect101(y - 1, roi_h)) * W,
+                              frame + static_cast<long long>(y) * W,
+                              frame + static_cast<long long>(reflect101(y + 1, roi_h)) * W};
+    uint32_t col01[kMaskPxPerThread + 2], col2[kMaskPxPerThread + 2];
+#pragma unroll
+    for (int i = 0; i < kMaskPxPerThread + 2; ++i) {
+        // columns right of the ROI are never used by a counted pixel; clamp keeps the load in range
+        const int xc = reflect101(min(x0 - 1 + i, roi_w), roi_w);
+        uint32_t a = 0, c = 0;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const uint2 e = cmap[rows[r][xc]];
+            a += e.x;
+            c += e.y;
+        }
+        col01[i] = a;
+        col2[i] = c;
+    }
+#pragma unroll
+    for (int j = 0; j < kMaskPxPerThread; ++j) {
+        if (j >= n_out) break;
+        uint8_t m = 0;
+        if (x0 + j < roi_w) {
+            const uint32_t s01 = col01[j] + col01[j + 1] + col01[j + 2], s2 = col2[j] + col2[j + 1] + col2[j + 2];
+            const uint32_t b0 = (2 * (s01 & 0xffffu) + 9) / 18, b1 = (2 * (s01 >> 16) + 9) / 18, b2 = (2 * s2 + 9) / 18;
+            m = ((b0 * 1868 + b1 * 9617 + b2 * 4899 + 8192) >> 14) > 127 ? 255 : 0;
+        }
+        out[j] = m;
+    }
 }
 
 }  // namespace
@@ -58,7 +82,7 @@ extern "C" int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int ro
     if (B == 0) return SSB_OK;
     if (!labels || !colormap || !mask) return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
     if (B > 65535 || (H + 7) / 8 > 65535) return fail(SSB_ERR_LIMIT, "B and H/8 must be <= 65535");
-    dim3 grid((W + 31) / 32, (H + 7) / 8, B);
+    dim3 grid((W + kMaskTileW - 1) / kMaskTileW, (H + kMaskTileH - 1) / kMaskTileH, B);
     fg_mask_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(labels, H, W, roi_h, roi_w, colormap, mask);
     SSB_CUDA_TRY(cudaGetLastError());
     return SSB_OK;

@@ -58,16 +58,19 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
             uint8_t *o = dst + dphase + x * 3;
             o[0] = r; o[1] = g; o[2] = bl;
         }
-    } else {
-        for (int i = tid; i < out_bytes; i += kPreThreads) dst[dphase + i] = 0;
     }
-    __syncthreads();
-
     const int ohead = min(out_bytes, (16 - dphase) & 15);
     const int obody16 = (out_bytes - ohead) >> 4;
+    uint4 *o4 = reinterpret_cast<uint4 *>(grow + ohead);
+    if (y >= new_h) {  // padding row (ImageOps.expand): zeros straight to global memory
+        for (int i = tid; i < ohead; i += kPreThreads) grow[i] = 0;
+        for (int i = tid; i < obody16; i += kPreThreads) o4[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = ohead + obody16 * 16 + tid; i < out_bytes; i += kPreThreads) grow[i] = 0;
+        return;
+    }
+    __syncthreads();
     for (int i = tid; i < ohead; i += kPreThreads) grow[i] = dst[dphase + i];
     const uint4 *d4 = reinterpret_cast<const uint4 *>(dst + dphase + ohead);
-    uint4 *o4 = reinterpret_cast<uint4 *>(grow + ohead);
     for (int i = tid; i < obody16; i += kPreThreads) o4[i] = d4[i];
     for (int i = ohead + obody16 * 16 + tid; i < out_bytes; i += kPreThreads) grow[i] = dst[dphase + i];
 }
