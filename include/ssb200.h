@@ -68,7 +68,8 @@ SSB_API const char *ssb_last_error(void);
  *   frames_bgr   [B][Hc][Wc][3] u8, frame b at frames_bgr + b*frame_stride (bytes, >= Hc*Wc*3)
  *   xtab, ytab   int32[new_w], int32[new_h]: source column / row of each destination column / row
  *                (Pillow's accumulated-double NEAREST tables, built on the host by the caller --
- *                 semseg host module `nearest_index_table`; values in [0,Wc) / [0,Hc))
+ *                 semseg host module `nearest_index_table`; values in [0,Wc) / [0,Hc)); xtab must be
+ *                 16-byte aligned (any device allocation is)
  *   out_rgb      [B][H][W][3] u8, dense; pixels with x >= new_w or y >= new_h are zero
  *                (ImageOps.expand padding).  new_w <= W, new_h <= H.
  * The stretch branch (sem_seg_server.py:157-159) is the same call with new_w = W, new_h = H. */

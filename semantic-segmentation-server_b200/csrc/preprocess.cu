@@ -2,77 +2,117 @@
 // fused into one gather (replaces sem_seg_server.py:150-161: cv2.cvtColor, Image.fromarray,
 // edgetpu resampling_with_original_ratio(NEAREST) = Image.resize + ImageOps.expand, np.asarray().flatten()).
 //
-// One CTA per (frame, output row).  A sampled source row (Wc*3 bytes, 5760 B at 1080p) is staged in
-// shared memory with coalesced 128-bit loads -- every 32-byte sector of a sampled row is touched by
-// the 11.2-byte sample stride anyway, so reading the row densely costs no extra DRAM traffic and
-// makes the read side fully vectorised.  The output row (W*3 bytes, 1539 B: never 16-byte aligned
-// from row to row) is assembled in shared memory at the same 16-byte phase as its global address and
-// written back with 128-bit stores (byte stores only for the ragged head and tail).  Rows that are
-// pure padding (y >= new_h) skip the read entirely.  Index tables are built on the host
-// (Pillow accumulates `xo += scale` in double; see semseg host module nearest_index_table).
+// One WARP per (frame, output row), four independent warps per CTA, no block-wide barriers:
+//   1. the sampled source row (Wc*3 bytes, 5760 B at 1080p) is copied into the warp's shared memory
+//      with 16-byte cp.async transfers -- every 32-byte sector of a sampled row is touched by the
+//      11.2-byte sample stride anyway, so reading the row densely costs no extra DRAM traffic and
+//      makes the read side fully vectorised and coalesced;
+//   2. each lane gathers quads of pixels (source offsets from the host-built Pillow index table, one
+//      128-bit load per quad), swaps B and R while packing 12 bytes into three words, and stores them
+//      word-wise into a staging row;
+//   3. the output row (W*3 bytes, 1539 B: its 16-byte phase changes from row to row) leaves as
+//      128-bit global stores; the staging row is re-aligned to that phase on the way out with funnel
+//      shifts (byte stores only for the ragged head and tail).
+// Rows that are pure padding (y >= new_h, ImageOps.expand) skip 1-2 and store zeros.  Index tables
+// are built on the host (Pillow accumulates `xo += scale` in double; see the host module's
+// nearest_index_table).  An earlier version used one CTA per row with byte-wise staging and was
+// issue-bound (65 % issue slots at 30 % DRAM utilisation).
 #include "ssb_common.cuh"
 
 namespace ssb {
 namespace {
 
-constexpr int kPreThreads = 128;
+constexpr int kPreWarps = 4, kPreThreads = kPreWarps * 32;
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __global__ void __launch_bounds__(kPreThreads)
 preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_stride, int Wc,
                           const int *__restrict__ xtab, const int *__restrict__ ytab, int new_w, int new_h,
-                          uint8_t *__restrict__ out, int H, int W, int src_smem_bytes) {
+                          uint8_t *__restrict__ out, int H, int W, int rows_total, int src_bytes, int dst_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint8_t *src = smem;                       // [<= 15 B phase][Wc*3], 16-byte phase of the global row
-    uint8_t *dst = smem + src_smem_bytes;      // [<= 15 B phase][W*3]
-    const int y = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
-    const int out_bytes = W * 3;
-    uint8_t *grow = out + (static_cast<long long>(b) * H + y) * out_bytes;
-    const int dphase = static_cast<int>(reinterpret_cast<uintptr_t>(grow) & 15);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int row = blockIdx.x * kPreWarps + warp;          // flat (frame, output row)
+    if (row >= rows_total) return;
+    const int b = row / H, y = row - b * H;
+    uint8_t *src = smem + warp * (src_bytes + dst_bytes);    // [<= 15 B phase][Wc*3]
+    uint32_t *dst = reinterpret_cast<uint32_t *>(src + src_bytes);   // [W*3 rounded up to words + spare]
 
-    if (y < new_h) {
-        const int row_bytes = Wc * 3;
-        const uint8_t *srow = frames + b * frame_stride + static_cast<long long>(ytab[y]) * row_bytes;
-        const int sphase = static_cast<int>(reinterpret_cast<uintptr_t>(srow) & 15);
-        // head (to the next 16-byte boundary), 128-bit body, tail
-        const int head = min(row_bytes, (16 - sphase) & 15);
-        const int body16 = (row_bytes - head) >> 4;
-        for (int i = tid; i < head; i += kPreThreads) src[sphase + i] = srow[i];
-        const uint4 *g4 = reinterpret_cast<const uint4 *>(srow + head);
-        uint4 *s4 = reinterpret_cast<uint4 *>(src + sphase + head);
-        for (int i = tid; i < body16; i += kPreThreads) {
-            uint4 v;
-            asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                         : "l"(g4 + i));
-            s4[i] = v;
-        }
-        for (int i = head + body16 * 16 + tid; i < row_bytes; i += kPreThreads) src[sphase + i] = srow[i];
-        __syncthreads();
-        const uint8_t *sp = src + sphase;
-        for (int x = tid; x < W; x += kPreThreads) {
-            uint8_t r = 0, g = 0, bl = 0;
-            if (x < new_w) {
-                const uint8_t *px = sp + xtab[x] * 3;  // source is B,G,R
-                bl = px[0]; g = px[1]; r = px[2];
-            }
-            uint8_t *o = dst + dphase + x * 3;
-            o[0] = r; o[1] = g; o[2] = bl;
-        }
-    }
+    const int out_bytes = W * 3;
+    uint8_t *grow = out + static_cast<long long>(row) * out_bytes;
+    const int dphase = static_cast<int>(reinterpret_cast<uintptr_t>(grow) & 15);
     const int ohead = min(out_bytes, (16 - dphase) & 15);
     const int obody16 = (out_bytes - ohead) >> 4;
     uint4 *o4 = reinterpret_cast<uint4 *>(grow + ohead);
-    if (y >= new_h) {  // padding row (ImageOps.expand): zeros straight to global memory
-        for (int i = tid; i < ohead; i += kPreThreads) grow[i] = 0;
-        for (int i = tid; i < obody16; i += kPreThreads) o4[i] = make_uint4(0u, 0u, 0u, 0u);
-        for (int i = ohead + obody16 * 16 + tid; i < out_bytes; i += kPreThreads) grow[i] = 0;
+
+    if (y >= new_h) {  // padding row: zeros straight to global memory
+        for (int i = lane; i < ohead; i += 32) grow[i] = 0;
+        for (int i = lane; i < obody16; i += 32) o4[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = ohead + obody16 * 16 + lane; i < out_bytes; i += 32) grow[i] = 0;
         return;
     }
-    __syncthreads();
-    for (int i = tid; i < ohead; i += kPreThreads) grow[i] = dst[dphase + i];
-    const uint4 *d4 = reinterpret_cast<const uint4 *>(dst + dphase + ohead);
-    for (int i = tid; i < obody16; i += kPreThreads) o4[i] = d4[i];
-    for (int i = ohead + obody16 * 16 + tid; i < out_bytes; i += kPreThreads) grow[i] = dst[dphase + i];
+
+    // 1. source row -> shared memory (same 16-byte phase as in global memory)
+    const int row_bytes = Wc * 3;
+    const uint8_t *srow = frames + b * frame_stride + static_cast<long long>(ytab[y]) * row_bytes;
+    const int sphase = static_cast<int>(reinterpret_cast<uintptr_t>(srow) & 15);
+    const int head = min(row_bytes, (16 - sphase) & 15);
+    const int body16 = (row_bytes - head) >> 4;
+    uint8_t *sp = src + sphase;
+    for (int i = lane; i < head; i += 32) sp[i] = srow[i];
+    for (int i = lane; i < body16; i += 32) cp_async16(sp + head + i * 16, srow + head + i * 16);
+    for (int i = head + body16 * 16 + lane; i < row_bytes; i += 32) sp[i] = srow[i];
+    cp_async_wait_all();
+    __syncwarp();
+
+    // 2. gather: quads of output pixels -> three packed words each
+    const int quads = (W + 3) >> 2;
+    for (int q = lane; q < quads; q += 32) {
+        const int x0 = q * 4;
+        int xs[4];
+        if (x0 + 3 < new_w) {
+            const int4 t = *reinterpret_cast<const int4 *>(xtab + x0);   // table is 16-byte aligned (x0 % 4 == 0)
+            xs[0] = t.x; xs[1] = t.y; xs[2] = t.z; xs[3] = t.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) xs[j] = x0 + j < new_w ? xtab[x0 + j] : -1;
+        }
+        uint32_t px[4];   // R | G<<8 | B<<16 of each pixel (source order is B,G,R)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (xs[j] >= 0) {
+                const uint8_t *p = sp + xs[j] * 3;
+                px[j] = static_cast<uint32_t>(p[2]) | (static_cast<uint32_t>(p[1]) << 8) | (static_cast<uint32_t>(p[0]) << 16);
+            } else {
+                px[j] = 0u;   // right of the resized image: ImageOps.expand padding
+            }
+        }
+        // 12 bytes R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+        dst[3 * q + 0] = px[0] | (px[1] << 24);
+        dst[3 * q + 1] = (px[1] >> 8) | (px[2] << 16);
+        dst[3 * q + 2] = (px[2] >> 16) | (px[3] << 8);
+    }
+    __syncwarp();
+
+    // 3. staging row -> global: byte head, 128-bit body re-aligned by (ohead mod 4) bytes, byte tail
+    const uint8_t *dbytes = reinterpret_cast<const uint8_t *>(dst);
+    for (int i = lane; i < ohead; i += 32) grow[i] = dbytes[i];
+    const int wsh = (ohead & 3) * 8;          // bit offset of the body inside the staging words
+    const uint32_t *dw = dst + (ohead >> 2);  // first staging word that holds body bytes
+    for (int i = lane; i < obody16; i += 32) {
+        const uint32_t *w = dw + 4 * i;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
+        uint4 v;
+        v.x = __funnelshift_r(w0, w1, wsh);
+        v.y = __funnelshift_r(w1, w2, wsh);
+        v.z = __funnelshift_r(w2, w3, wsh);
+        v.w = __funnelshift_r(w3, w4, wsh);
+        o4[i] = v;
+    }
+    for (int i = ohead + obody16 * 16 + lane; i < out_bytes; i += 32) grow[i] = dbytes[i];
 }
 
 }  // namespace
@@ -90,18 +130,21 @@ extern "C" int ssb_preprocess_nearest_u8(const uint8_t *frames_bgr, int B, int H
         return fail(SSB_ERR_BAD_SHAPE, "frame_stride %lld < Hc*Wc*3", static_cast<long long>(frame_stride));
     if (B == 0) return SSB_OK;
     if (!frames_bgr || !xtab || !ytab || !out_rgb) return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
-    if (H > 65535 || B > 65535) return fail(SSB_ERR_LIMIT, "H and B must be <= 65535");
-    const int src_smem = ((Wc * 3 + 15 + 15) / 16) * 16;
-    const int dst_smem = ((W * 3 + 15 + 15) / 16) * 16;
-    const int smem = src_smem + dst_smem;
+    if (reinterpret_cast<uintptr_t>(xtab) % 16 != 0) return fail(SSB_ERR_BAD_POINTER, "xtab must be 16-byte aligned");
+    const long long rows_total = static_cast<long long>(B) * H;
+    if (rows_total >= (1ll << 31)) return fail(SSB_ERR_LIMIT, "B*H must be < 2^31");
+    const int src_bytes = ((Wc * 3 + 15 + 15) / 16) * 16;
+    const int dst_bytes = (((W + 3) / 4 * 12 + 16 + 15) / 16) * 16;   // whole quads + spare words for the funnel
+    const int smem = kPreWarps * (src_bytes + dst_bytes);
     DeviceInfo di;
     if (int rc = device_info(&di)) return rc;
     if (smem > di.max_smem_optin) return fail(SSB_ERR_LIMIT, "row of %d px needs %d B shared memory", Wc, smem);
     if (smem > 48 * 1024)
         SSB_CUDA_TRY(cudaFuncSetAttribute(preprocess_nearest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    dim3 grid(H, B);
+    const unsigned grid = static_cast<unsigned>((rows_total + kPreWarps - 1) / kPreWarps);
     preprocess_nearest_kernel<<<grid, kPreThreads, smem, static_cast<cudaStream_t>(stream)>>>(
-        frames_bgr, frame_stride, Wc, xtab, ytab, new_w, new_h, out_rgb, H, W, src_smem);
+        frames_bgr, frame_stride, Wc, xtab, ytab, new_w, new_h, out_rgb, H, W, static_cast<int>(rows_total), src_bytes,
+        dst_bytes);
     SSB_CUDA_TRY(cudaGetLastError());
     return SSB_OK;
 }
