@@ -130,6 +130,10 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_stream_kernel(
     const long long t0 = p.n_tiles * blockIdx.x / gridDim.x;
     const long long t1 = p.n_tiles * (blockIdx.x + 1) / gridDim.x;
 
+    // Let the next kernel in the stream (typically the next batch's launch of this same kernel) place
+    // its CTAs on SMs as ours retire and run its prologue early.
+    pdl_trigger();
+
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full[s], 1);
@@ -143,6 +147,10 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_stream_kernel(
         for (int i = tid; i < (K::kHistBytes + K::kBlkBytes) / 8; i += K::kThreads) z[i] = 0ull;
     }
     __syncthreads();
+    // Everything above touched shared memory only.  From here on global memory is read and written:
+    // wait until the kernels this launch depends on have completed and their writes are visible
+    // (a no-op when the launch was not programmatic).
+    pdl_wait();
 
     if (warp == NWARPS) {
         // ===== producer: one elected lane streams this CTA's span through the ring =====
@@ -362,8 +370,7 @@ int launch_stream(const ArgmaxParams &base, cudaStream_t st) {
     long long grid = static_cast<long long>(di.sm_count) * ctas_per_sm[dev];
     if (const char *env = getenv("SSB_ARGMAX_WAVES")) grid *= atoi(env) > 0 ? atoi(env) : 1;  // tuning knob
     if (grid > p.n_tiles) grid = p.n_tiles > 0 ? p.n_tiles : 1;
-    kern<<<static_cast<unsigned>(grid), K::kThreads, K::kSmem, st>>>(p);
-    SSB_CUDA_TRY(cudaGetLastError());
+    SSB_CUDA_TRY(launch_pdl(kern, dim3(static_cast<unsigned>(grid)), dim3(K::kThreads), K::kSmem, st, p));
     return SSB_OK;
 }
 

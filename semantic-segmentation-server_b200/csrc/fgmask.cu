@@ -26,6 +26,8 @@ __global__ void __launch_bounds__(256)
 fg_mask_kernel(const uint8_t *__restrict__ labels, int H, int W, int roi_h, int roi_w,
                const uint8_t *__restrict__ colormap, uint8_t *__restrict__ mask) {
     __shared__ uint2 cmap[256];  // .x = c0 | c1<<16, .y = c2
+    pdl_trigger();
+    pdl_wait();
     for (int i = threadIdx.x; i < 256; i += blockDim.x)
         cmap[i] = make_uint2(colormap[3 * i] | (colormap[3 * i + 1] << 16), colormap[3 * i + 2]);
     __syncthreads();
@@ -83,7 +85,7 @@ extern "C" int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int ro
     if (!labels || !colormap || !mask) return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
     if (B > 65535 || (H + 7) / 8 > 65535) return fail(SSB_ERR_LIMIT, "B and H/8 must be <= 65535");
     dim3 grid((W + kMaskTileW - 1) / kMaskTileW, (H + kMaskTileH - 1) / kMaskTileH, B);
-    fg_mask_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(labels, H, W, roi_h, roi_w, colormap, mask);
-    SSB_CUDA_TRY(cudaGetLastError());
+    SSB_CUDA_TRY(launch_pdl(fg_mask_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream), labels, H, W, roi_h,
+                            roi_w, colormap, mask));
     return SSB_OK;
 }

@@ -34,6 +34,8 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
                           const int *__restrict__ xtab, const int *__restrict__ ytab, int new_w, int new_h,
                           uint8_t *__restrict__ out, int H, int W, int rows_total, int src_bytes, int dst_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
+    pdl_trigger();
+    pdl_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row = blockIdx.x * kPreWarps + warp;          // flat (frame, output row)
     if (row >= rows_total) return;
@@ -142,9 +144,8 @@ extern "C" int ssb_preprocess_nearest_u8(const uint8_t *frames_bgr, int B, int H
     if (smem > 48 * 1024)
         SSB_CUDA_TRY(cudaFuncSetAttribute(preprocess_nearest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const unsigned grid = static_cast<unsigned>((rows_total + kPreWarps - 1) / kPreWarps);
-    preprocess_nearest_kernel<<<grid, kPreThreads, smem, static_cast<cudaStream_t>(stream)>>>(
-        frames_bgr, frame_stride, Wc, xtab, ytab, new_w, new_h, out_rgb, H, W, static_cast<int>(rows_total), src_bytes,
-        dst_bytes);
-    SSB_CUDA_TRY(cudaGetLastError());
+    SSB_CUDA_TRY(launch_pdl(preprocess_nearest_kernel, dim3(grid), dim3(kPreThreads), smem,
+                            static_cast<cudaStream_t>(stream), frames_bgr, static_cast<long long>(frame_stride), Wc, xtab,
+                            ytab, new_w, new_h, out_rgb, H, W, static_cast<int>(rows_total), src_bytes, dst_bytes));
     return SSB_OK;
 }

@@ -7,6 +7,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "ssb200.h"
 
@@ -49,6 +50,34 @@ struct WorkspaceLease {
 };
 int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out);
 int workspace_release(const WorkspaceLease &lease, cudaStream_t stream);
+
+// ---- programmatic dependent launch ---------------------------------------------------------------
+// Every kernel of the library (1) lets the NEXT kernel in the stream start placing CTAs while its own
+// CTAs retire (`pdl_trigger` at the top) and (2) waits for the kernels it depends on before touching
+// global memory (`pdl_wait`).  Launched through launch_pdl the wait sits behind whatever needs no
+// global memory (barrier init, shared-memory clears), which hides the ~1.5 us between two dependent
+// launches; semantics are those of ordinary stream order.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    const char *no_pdl = getenv("SSB_NO_PDL");   // tuning knob: "1" = plain stream-ordered launches
+    attr[0].val.programmaticStreamSerializationAllowed = (no_pdl && no_pdl[0] == '1') ? 0 : 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 // ---- device-side PTX wrappers ----------------------------------------------------------------
 #ifdef __CUDACC__
