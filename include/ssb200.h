@@ -158,6 +158,17 @@ SSB_API int ssb_pipeline_destroy(ssb_pipeline *p);
 SSB_API int ssb_pipeline_argmax_stats_host(ssb_pipeline *p, const void *logits_host, int B, int roi_h, int roi_w,
                                    uint8_t *labels_host, uint64_t *stats_host);
 
+/* Ingest pipeline for camera frames held on the host (cap.read(), sem_seg_server.py:144-152): frames go
+ * host -> device in chunks on `n_slots` streams, run through ssb_preprocess_nearest_u8 there, and the
+ * model inputs [B][H][W][3] come back to `out_rgb_host`; copies of chunk i+1 overlap the kernel of
+ * chunk i.  Replaces sem_seg_server.py:150-161 for a batch of host frames.  xtab/ytab are HOST tables
+ * (as for ssb_preprocess_nearest_u8); destroy with ssb_pipeline_destroy. */
+SSB_API int ssb_pipeline_create_ingest(ssb_pipeline **out, int Hc, int Wc, int H, int W, int max_frames_per_chunk,
+                                       int n_slots);
+SSB_API int ssb_pipeline_preprocess_host(ssb_pipeline *p, const uint8_t *frames_bgr_host, int B,
+                                         const int32_t *xtab_host, const int32_t *ytab_host, int new_w, int new_h,
+                                         uint8_t *out_rgb_host);
+
 #ifdef __cplusplus
 }
 #endif

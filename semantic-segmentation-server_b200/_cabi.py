@@ -30,6 +30,9 @@ SIGNATURES = {
                                 _c_void_p]),
     "ssb_pipeline_create": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),
     "ssb_pipeline_destroy": (_c_int, [_c_void_p]),
+    "ssb_pipeline_create_ingest": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),
+    "ssb_pipeline_preprocess_host": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_void_p, _c_void_p, _c_int, _c_int,
+                                              _c_void_p]),
     "ssb_pipeline_argmax_stats_host": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_void_p,
                                                 _c_void_p]),
 }

@@ -9,11 +9,13 @@
 
 struct ssb_pipeline {
     int device, H, W, C, elem_bytes, max_frames, n_slots;
+    int cam_h, cam_w;            // > 0: ingest pipeline (camera frames -> model input), else logits pipeline
     size_t frame_in_bytes, frame_px;
+    int32_t *d_xtab, *d_ytab;    // ingest only: device copies of the index tables of the last call
     struct Slot {
         cudaStream_t stream;
-        void *d_logits;
-        uint8_t *d_labels;
+        void *d_logits;          // logits chunk, or camera frames chunk (ingest)
+        uint8_t *d_labels;       // label maps, or model inputs (ingest)
         uint64_t *d_stats;
     } *slots;
 };
@@ -34,6 +36,8 @@ extern "C" int ssb_pipeline_destroy(ssb_pipeline *p) {
         }
         delete[] p->slots;
     }
+    cudaFree(p->d_xtab);
+    cudaFree(p->d_ytab);
     delete p;
     cudaSetDevice(prev);
     return SSB_OK;
@@ -105,4 +109,79 @@ extern "C" int ssb_pipeline_argmax_stats_host(ssb_pipeline *p, const void *logit
     }
     for (int i = 0; i < p->n_slots; ++i) SSB_CUDA_TRY(cudaStreamSynchronize(p->slots[i].stream));
     return SSB_OK;
+}
+
+// ---- ingest: camera frames held on the host -> model inputs (row f3 of SURVEY.md section 8) ----------
+extern "C" int ssb_pipeline_create_ingest(ssb_pipeline **out, int Hc, int Wc, int H, int W, int max_frames_per_chunk,
+                                          int n_slots) {
+    using namespace ssb;
+    if (!out) return fail(SSB_ERR_BAD_POINTER, "out is NULL");
+    *out = nullptr;
+    if (Hc <= 0 || Wc <= 0 || H <= 0 || W <= 0 || max_frames_per_chunk < 1 || n_slots < 1 || n_slots > 16)
+        return fail(SSB_ERR_BAD_SHAPE, "bad ingest geometry");
+    ssb_pipeline *p = new (std::nothrow) ssb_pipeline();
+    if (!p) return fail(SSB_ERR_LIMIT, "out of host memory");
+    p->H = H; p->W = W; p->C = 3; p->elem_bytes = 1; p->cam_h = Hc; p->cam_w = Wc;
+    p->max_frames = max_frames_per_chunk; p->n_slots = n_slots;
+    p->frame_px = static_cast<size_t>(H) * W * 3;                 // bytes of one model input
+    p->frame_in_bytes = static_cast<size_t>(Hc) * Wc * 3;         // bytes of one camera frame
+    p->slots = new (std::nothrow) ssb_pipeline::Slot[n_slots]();
+    cudaError_t e = cudaGetDevice(&p->device);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_xtab, sizeof(int32_t) * W);
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_ytab, sizeof(int32_t) * H);
+    for (int i = 0; e == cudaSuccess && p->slots && i < n_slots; ++i) {
+        auto &s = p->slots[i];
+        e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaMalloc(&s.d_logits, p->frame_in_bytes * max_frames_per_chunk);
+        if (e == cudaSuccess) e = cudaMalloc(&s.d_labels, p->frame_px * max_frames_per_chunk);
+    }
+    if (e != cudaSuccess || !p->slots) {
+        ssb_pipeline_destroy(p);
+        return fail(SSB_ERR_CUDA, "ingest pipeline allocation failed: %s", cudaGetErrorString(e));
+    }
+    *out = p;
+    return SSB_OK;
+}
+
+extern "C" int ssb_pipeline_preprocess_host(ssb_pipeline *p, const uint8_t *frames_bgr_host, int B,
+                                            const int32_t *xtab_host, const int32_t *ytab_host, int new_w, int new_h,
+                                            uint8_t *out_rgb_host) {
+    using namespace ssb;
+    if (!p || p->cam_h <= 0) return fail(SSB_ERR_BAD_POINTER, "not an ingest pipeline");
+    if (B < 0) return fail(SSB_ERR_BAD_SHAPE, "B=%d", B);
+    if (new_w < 1 || new_w > p->W || new_h < 1 || new_h > p->H)
+        return fail(SSB_ERR_BAD_SHAPE, "resized size (%d,%d) outside model input (%d,%d)", new_w, new_h, p->W, p->H);
+    if (B == 0) return SSB_OK;
+    if (!frames_bgr_host || !xtab_host || !ytab_host || !out_rgb_host) return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
+    int dev = 0;
+    SSB_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev != p->device) return fail(SSB_ERR_BAD_SHAPE, "pipeline belongs to device %d, current is %d", p->device, dev);
+    // tables first, on slot 0's stream; the other slots wait for them through an event
+    cudaStream_t s0 = p->slots[0].stream;
+    SSB_CUDA_TRY(cudaMemcpyAsync(p->d_xtab, xtab_host, sizeof(int32_t) * new_w, cudaMemcpyHostToDevice, s0));
+    SSB_CUDA_TRY(cudaMemcpyAsync(p->d_ytab, ytab_host, sizeof(int32_t) * new_h, cudaMemcpyHostToDevice, s0));
+    cudaEvent_t tables;
+    SSB_CUDA_TRY(cudaEventCreateWithFlags(&tables, cudaEventDisableTiming));
+    SSB_CUDA_TRY(cudaEventRecord(tables, s0));
+    for (int i = 1; i < p->n_slots; ++i) SSB_CUDA_TRY(cudaStreamWaitEvent(p->slots[i].stream, tables, 0));
+    int rc = SSB_OK, chunk = 0;
+    for (int b0 = 0; b0 < B && rc == SSB_OK; b0 += p->max_frames, ++chunk) {
+        const int nb = B - b0 < p->max_frames ? B - b0 : p->max_frames;
+        auto &s = p->slots[chunk % p->n_slots];
+        cudaError_t e = cudaMemcpyAsync(s.d_logits, frames_bgr_host + p->frame_in_bytes * b0, p->frame_in_bytes * nb,
+                                        cudaMemcpyHostToDevice, s.stream);
+        if (e != cudaSuccess) { rc = fail(SSB_ERR_CUDA, "H2D copy failed: %s", cudaGetErrorString(e)); break; }
+        rc = ssb_preprocess_nearest_u8(static_cast<const uint8_t *>(s.d_logits), nb, p->cam_h, p->cam_w,
+                                       static_cast<int64_t>(p->frame_in_bytes), p->d_xtab, p->d_ytab, new_w, new_h,
+                                       s.d_labels, p->H, p->W, s.stream);
+        if (rc) break;
+        e = cudaMemcpyAsync(out_rgb_host + p->frame_px * b0, s.d_labels, p->frame_px * nb, cudaMemcpyDeviceToHost, s.stream);
+        if (e != cudaSuccess) rc = fail(SSB_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e));
+    }
+    for (int i = 0; i < p->n_slots; ++i) {
+        const cudaError_t e = cudaStreamSynchronize(p->slots[i].stream);
+        if (e != cudaSuccess && rc == SSB_OK) rc = fail(SSB_ERR_CUDA, "stream sync failed: %s", cudaGetErrorString(e));
+    }
+    cudaEventDestroy(tables);
+    return rc;
 }

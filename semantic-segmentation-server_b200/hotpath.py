@@ -268,3 +268,39 @@ class HostPipeline:
             self.close()
         except Exception:
             pass
+
+
+class IngestPipeline:
+    """Owns an ingest ssb_pipeline: camera frames in host memory -> model inputs in host memory,
+    through K1 on the GPU with copies and kernels overlapped (sem_seg_server.py:144-161 for a batch)."""
+
+    def __init__(self, geom, frames_per_chunk=16, n_slots=3, device=0):
+        import ctypes
+        self.geom, self.device = geom, device
+        self._p = ctypes.c_void_p()
+        with torch.cuda.device(device):
+            _cabi.check(_cabi.lib.ssb_pipeline_create_ingest(ctypes.byref(self._p), geom.cam_h, geom.cam_w, geom.height,
+                                                             geom.width, frames_per_chunk, n_slots))
+
+    def preprocess(self, frames_bgr_host, out=None):
+        a, g = frames_bgr_host, self.geom
+        if not (isinstance(a, np.ndarray) and a.flags.c_contiguous and a.dtype == np.uint8
+                and a.shape[1:] == (g.cam_h, g.cam_w, 3)):
+            raise ValueError("frames must be a C-contiguous [B,%d,%d,3] uint8 array" % (g.cam_h, g.cam_w))
+        if out is None:
+            out = np.empty((a.shape[0], g.height, g.width, 3), np.uint8)
+        with torch.cuda.device(self.device):
+            _cabi.check(_cabi.lib.ssb_pipeline_preprocess_host(self._p, a.ctypes.data, a.shape[0], g.xtab.ctypes.data,
+                                                               g.ytab.ctypes.data, g.new_w, g.new_h, out.ctypes.data))
+        return out
+
+    def close(self):
+        if self._p:
+            _cabi.lib.ssb_pipeline_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -379,6 +379,21 @@ def test_host_pipeline_matches_device_path(ssb):
     assert (labels == want[0]).all() and (stats == want[1]).all()
 
 
+def test_ingest_pipeline_host_frames(ssb):
+    """Row f3: camera frames in host memory -> model inputs, chunked over streams."""
+    frames = np.random.default_rng(43).integers(0, 256, (11, 480, 640, 3), dtype=np.uint8)
+    geom = ssb.FrameGeometry(640, 480, 513, 513)
+    pipe = ssb.IngestPipeline(geom, frames_per_chunk=4, n_slots=2)
+    out = pipe.preprocess(frames)
+    for i in range(11):
+        assert (out[i] == sp.preprocess_frame(frames[i], 513, 513)[0]).all()
+    out2 = pipe.preprocess(frames[:3])                    # reuse
+    assert (out2 == out[:3]).all()
+    pipe.close()
+    with pytest.raises(ValueError):
+        ssb.IngestPipeline(geom).preprocess(frames[:, :100])
+
+
 def test_raw_cabi_call_with_ctypes(ssb):
     """The call a non-torch host would make: raw device pointers from cudaMalloc via the runtime."""
     q = np.random.default_rng(42).integers(0, 256, (2, 65, 65, 21), dtype=np.uint8)
