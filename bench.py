@@ -182,6 +182,25 @@ def other_kernels(ssb200, torch):
     us = _time_us(torch, lambda i: ssb200.foreground_mask(labels, ROI_H, ROI_W, cm, out=mask), 20)
     out.append({"kernel": "fg_mask (513x513, batch 64)", "us": us, "frames_per_s": b / us * 1e6,
                 "GBps": 2 * H * W * b / us / 1e3})
+    # config 1: one frame, K1 -> K2+K3, launch to completion (latency; the data is L2-resident)
+    f1 = torch.randint(0, 256, (1, H, W, 3), dtype=torch.uint8, device="cuda", generator=g)
+    g1 = ssb200.FrameGeometry(W, H, H, W)
+    q1 = torch.randint(0, 256, (1, H, W, C), dtype=torch.uint8, device="cuda", generator=g)
+    rgb1 = torch.empty((1, H, W, 3), dtype=torch.uint8, device="cuda")
+    lab1 = torch.empty((1, H, W), dtype=torch.uint8, device="cuda")
+    st1 = torch.empty((1, C, 4), dtype=torch.int64, device="cuda")
+
+    def one(i):
+        ssb200.preprocess_frames(f1, g1, out=rgb1)
+        ssb200.argmax_stats(q1, labels=lab1, stats=st1)
+    us = _time_us(torch, one, 200)
+    t0 = time.perf_counter()
+    for i in range(200):
+        one(i)
+        torch.cuda.synchronize()
+    wall_us = (time.perf_counter() - t0) / 200 * 1e6
+    out.append({"kernel": "config1: single 513x513 frame, preprocess + argmax_stats", "us_device_back_to_back": us,
+                "us_host_launch_to_sync": wall_us})
     return out
 
 
@@ -196,6 +215,7 @@ def run_ssb(args):
     if world != args.gpus:
         raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (args.gpus, world))
     torch.cuda.set_device(local)
+    numa_cores = ssb200.bind_process_to_device_numa(local) if world > 1 else 0   # pinned buffers next to the GPU
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -313,7 +333,8 @@ def run_ssb(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "frames_per_gpu_per_step": BATCH,
                        "l2": "inputs larger than L2: %d distinct 354 MB batches rotated, no flush" % N_ROTATE,
-                       "sharding": "frames by GPU, no collective"},
+                       "sharding": "frames by GPU, no collective",
+                       "host_numa_binding_cores_rank0": numa_cores},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "argmax_stats_stream_kernel<CodecU8<21>,8,3>",

@@ -7,6 +7,6 @@ from .hotpath import (Centroid, FrameGeometry, HostPipeline, IngestPipeline, Seg
                       nearest_index_table, normalise, objects_from_contours, objects_from_stats,
                       preprocess_frames)
 
-from .scheduler import FrameScheduler, aligned_chunks, partition_frames  # noqa: F401
+from .scheduler import FrameScheduler, aligned_chunks, bind_process_to_device_numa, partition_frames  # noqa: F401
 
 __version__ = "0.1.0"

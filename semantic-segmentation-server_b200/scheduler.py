@@ -33,6 +33,25 @@ def aligned_chunks(start, stop, chunk, align=16):
     return [(s, min(stop, s + chunk)) for s in range(start, stop, chunk)]
 
 
+def bind_process_to_device_numa(device_index):
+    """Pins this process to the CPU cores closest to GPU `device_index` (NVML's ideal CPU affinity), so
+    that pinned host buffers allocated afterwards live on the GPU's NUMA node.  One process per GPU:
+    call it before allocating pinned memory.  Returns the core count, or 0 if NVML is unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, n_words)
+        cores = {64 * w + b for w, word in enumerate(mask) for b in range(64) if (word >> b) & 1}
+        cores &= os.sched_getaffinity(0)
+        if cores:
+            os.sched_setaffinity(0, cores)
+        return len(cores)
+    except Exception:
+        return 0
+
+
 class FrameScheduler:
     """One instance per process (= per GPU).  `world`/`rank` default to the torchrun environment."""
 

@@ -309,6 +309,47 @@ def test_preprocess_ragged_sizes(ssb, cam):
     assert (out == np.stack([sp.preprocess_frame(f, 33, 33, False)[0] for f in frames])).all()
 
 
+def test_preprocess_hypothesis_sizes(ssb):
+    from hypothesis import given, settings, strategies as st_
+
+    @settings(max_examples=40, deadline=None)
+    @given(cw=st_.integers(1, 300), ch=st_.integers(1, 200), W=st_.integers(1, 150), H=st_.integers(1, 150),
+           b=st_.integers(1, 3), keep=st_.booleans(), seed=st_.integers(0, 2 ** 31))
+    def prop(cw, ch, W, H, b, keep, seed):
+        frames = np.random.default_rng(seed).integers(0, 256, (b, ch, cw, 3), dtype=np.uint8)
+        try:
+            want = np.stack([sp.preprocess_frame(f, W, H, keep)[0] for f in frames])
+        except ValueError:                                   # frame collapses to zero pixels
+            with pytest.raises(ValueError):
+                ssb.FrameGeometry(cw, ch, W, H, keep)
+            return
+        out, _ = gpu_preprocess(ssb, frames, W, H, keep)
+        assert (out == want).all()
+    prop()
+
+
+def test_preprocess_strided_frames_and_views(ssb):
+    """Frames embedded in a larger buffer (frame_stride > Hc*Wc*3) and output written into a view."""
+    lib = ssb._cabi.lib
+    rng = np.random.default_rng(44)
+    b, ch, cw, W, H = 4, 37, 53, 40, 30
+    frames = rng.integers(0, 256, (b, ch, cw, 3), dtype=np.uint8)
+    stride = ch * cw * 3 + 37                                # odd padding between frames
+    buf = torch.zeros(b * stride + 5, dtype=torch.uint8, device="cuda")
+    for i in range(b):
+        buf[3 + i * stride: 3 + i * stride + ch * cw * 3] = torch.from_numpy(frames[i].ravel()).cuda()
+    geom = ssb.FrameGeometry(cw, ch, W, H)
+    xt, yt = geom.device_tables(torch.device("cuda", 0))
+    out = torch.full((b * H * W * 3 + 7,), 0xAB, dtype=torch.uint8, device="cuda")
+    rc = lib.ssb_preprocess_nearest_u8(buf.data_ptr() + 3, b, ch, cw, stride, xt.data_ptr(), yt.data_ptr(), geom.new_w,
+                                       geom.new_h, out.data_ptr() + 7, H, W, None)
+    assert rc == 0, lib.ssb_last_error()
+    torch.cuda.synchronize()
+    got = out[7:].cpu().numpy().reshape(b, H, W, 3)
+    assert (got == np.stack([sp.preprocess_frame(f, W, H)[0] for f in frames])).all()
+    assert (out[:7].cpu().numpy() == 0xAB).all()             # nothing written in front of the view
+
+
 # ---- foreground mask + reference-literal objects (f1) --------------------------------------------------
 def test_fg_mask_matches_reference_fixtures(ssb, golden):
     g = golden("objects.npz")
