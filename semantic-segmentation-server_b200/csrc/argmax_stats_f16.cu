@@ -150,6 +150,9 @@ struct CodecF16 {
 
 template <int C>
 int dispatch_cfg(const ArgmaxParams &p, cudaStream_t st, int nw, int stg) {
+    if (nw == 4 && stg == 2) return launch_stream<CodecF16<C>, 4, 2>(p, st);
+    if (nw == 2 && stg == 2) return launch_stream<CodecF16<C>, 2, 2>(p, st);
+    if (nw == 2 && stg == 3) return launch_stream<CodecF16<C>, 2, 3>(p, st);
     if (nw == 4 && stg == 3) return launch_stream<CodecF16<C>, 4, 3>(p, st);
     if (nw == 4 && stg == 4) return launch_stream<CodecF16<C>, 4, 4>(p, st);
     if (nw == 8 && stg == 2) return launch_stream<CodecF16<C>, 8, 2>(p, st);

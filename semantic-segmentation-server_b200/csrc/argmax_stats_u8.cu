@@ -148,13 +148,17 @@ struct CodecU8 {
 
 template <int C>
 int dispatch_cfg(const ArgmaxParams &p, cudaStream_t st, int nw, int stg) {
+    if (nw == 4 && stg == 2) return launch_stream<CodecU8<C>, 4, 2>(p, st);
     if (nw == 4 && stg == 3) return launch_stream<CodecU8<C>, 4, 3>(p, st);
+    if (nw == 8 && stg == 2) return launch_stream<CodecU8<C>, 8, 2>(p, st);
     if (nw == 4 && stg == 4) return launch_stream<CodecU8<C>, 4, 4>(p, st);
     if (nw == 8 && stg == 3) return launch_stream<CodecU8<C>, 8, 3>(p, st);
     return fail(SSB_ERR_LIMIT, "no kernel compiled for NWARPS=%d STAGES=%d", nw, stg);
 }
 
-constexpr int kDefaultWarps = 8, kDefaultStages = 3;   // best of the compiled set on B200 (tools/sweep_argmax.py)
+// Best of the compiled set on B200 (tools/sweep_argmax.py): 4 consumer warps, 2 stages = 46 KB per CTA,
+// 4 CTAs per SM, 86 KB in flight per SM.  Deeper rings or more bytes in flight are slower.
+constexpr int kDefaultWarps = 4, kDefaultStages = 2;
 
 }  // namespace
 }  // namespace ssb

@@ -107,7 +107,7 @@ def test_u8_kernel_configs_agree(ssb, monkeypatch):
     """Every compiled pipeline configuration and the generic kernel give identical bytes."""
     q = np.random.default_rng(11).integers(0, 256, (5, 513, 513, 21), dtype=np.uint8)
     want = cport.argmax_stats(q, 288, 513, threads=8)
-    for cfg in ["4,3", "4,4", "8,3", "generic"]:
+    for cfg in ["4,2", "4,3", "4,4", "8,2", "8,3", "generic"]:
         monkeypatch.setenv("SSB_ARGMAX_CFG", cfg)
         labels, stats = run_gpu(ssb, q, 288, 513)
         assert (labels == want[0]).all() and (stats == want[1]).all(), cfg
@@ -247,7 +247,7 @@ def test_f16_ties_and_infinities(ssb):
 def test_f16_kernel_configs_agree(ssb, monkeypatch):
     h = (np.random.default_rng(51).standard_normal((2, 300, 400, 19), dtype=np.float32)).astype(np.float16)
     want = cport.argmax_stats(h, 250, 400, threads=8)
-    for cfg in ["4,3", "4,4", "8,2", "generic"]:
+    for cfg in ["4,2", "2,2", "2,3", "4,3", "4,4", "8,2", "generic"]:
         monkeypatch.setenv("SSB_ARGMAX_F16_CFG", cfg)
         labels, stats = run_gpu(ssb, h, 250, 400)
         assert (labels == want[0]).all() and (stats == want[1]).all(), cfg
