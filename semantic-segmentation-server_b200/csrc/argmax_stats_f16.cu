@@ -83,38 +83,46 @@ struct CodecF16 {
         for (int j = 0; j < 4; ++j) key[j] = pixel_key(w, j, ctx);
     }
 
-    // Four 128-bit read-modify-writes: [packed n|Σk|Σj|Σdy : u64][Σ value*2^24 : i64]; loads first,
-    // addends forwarded between equal labels (see the u8 codec).
+    // value * 2^24 of a finite fp16 as an exact integer: fp16 -> fp32 and the scaling by a power of two
+    // are exact, so one F2I does it (the bit-twiddling form costs ~12 instructions per pixel).
+    static __device__ __forceinline__ long long fixed24(uint32_t hbits) {
+        const float f = __half2float(__ushort_as_half(static_cast<unsigned short>(hbits)));
+        return __float2ll_rn(f * 16777216.0f);
+    }
+
+    // 128-bit read-modify-writes of [packed n|Σk|Σj|Σdy : u64][Σ value*2^24 : i64] entries, two pixels
+    // at a time: both entries are loaded first and the second pixel adds the first one's addends itself
+    // when they share a label (its load is stale; its store, issued later to the same address, wins).
+    // Pairs instead of the u8 codec's quads: with two 64-bit words per entry, forwarding among four
+    // pixels costs more instructions than the second round of shared-memory latency.
+    static __device__ __forceinline__ void add2(uint32_t hist_lane, uint32_t key0, uint32_t key1, uint32_t lo_base,
+                                                uint32_t hi0, uint32_t hi1, bool c0, bool c1) {
+        const uint32_t addr0 = hist_lane - (key0 & 0xffu) * (32u * kEntryBytes);
+        const uint32_t addr1 = hist_lane - (key1 & 0xffu) * (32u * kEntryBytes);
+        const unsigned long long a0 = c0 ? ((static_cast<unsigned long long>(hi0) << 32) | lo_base) : 0ull;
+        const unsigned long long a1 = c1 ? ((static_cast<unsigned long long>(hi1) << 32) | lo_base) : 0ull;
+        const unsigned long long q0 = c0 ? static_cast<unsigned long long>(fixed24(key0 >> 16)) : 0ull;
+        const unsigned long long q1 = c1 ? static_cast<unsigned long long>(fixed24(key1 >> 16)) : 0ull;
+        uint32_t x0, x1, x2, x3, y0, y1, y2, y3;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(addr0));
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(y0), "=r"(y1), "=r"(y2), "=r"(y3) : "r"(addr1));
+        const unsigned long long va0 = ((static_cast<unsigned long long>(x1) << 32) | x0) + a0;
+        const unsigned long long vq0 = ((static_cast<unsigned long long>(x3) << 32) | x2) + q0;
+        const bool same = addr0 == addr1;
+        const unsigned long long va1 = ((static_cast<unsigned long long>(y1) << 32) | y0) + a1 + (same ? a0 : 0ull);
+        const unsigned long long vq1 = ((static_cast<unsigned long long>(y3) << 32) | y2) + q1 + (same ? q0 : 0ull);
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr0), "r"(static_cast<uint32_t>(va0)),
+                     "r"(static_cast<uint32_t>(va0 >> 32)), "r"(static_cast<uint32_t>(vq0)),
+                     "r"(static_cast<uint32_t>(vq0 >> 32)));
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr1), "r"(static_cast<uint32_t>(va1)),
+                     "r"(static_cast<uint32_t>(va1 >> 32)), "r"(static_cast<uint32_t>(vq1)),
+                     "r"(static_cast<uint32_t>(vq1 >> 32)));
+    }
+
     static __device__ __forceinline__ void add4(uint32_t hist_lane, const uint32_t (&key)[4], uint32_t lo_base,
                                                 const uint32_t (&add_hi)[4], const bool (&counted)[4]) {
-        uint32_t addr[4];
-        unsigned long long a[4], q[4], ea[4], eq[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            addr[j] = hist_lane - (key[j] & 0xffu) * (32u * kEntryBytes);
-            a[j] = counted[j] ? ((static_cast<unsigned long long>(add_hi[j]) << 32) | lo_base) : 0ull;
-            q[j] = counted[j] ? static_cast<unsigned long long>(half_bits_to_fixed24(key[j] >> 16)) : 0ull;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            uint32_t x0, x1, x2, x3;
-            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(addr[j]));
-            ea[j] = (static_cast<unsigned long long>(x1) << 32) | x0;
-            eq[j] = (static_cast<unsigned long long>(x3) << 32) | x2;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            unsigned long long va = ea[j] + a[j], vq = eq[j] + q[j];
-#pragma unroll
-            for (int i = 0; i < j; ++i) {
-                const bool same = addr[i] == addr[j];
-                va += same ? a[i] : 0ull;
-                vq += same ? q[i] : 0ull;
-            }
-            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr[j]), "r"(static_cast<uint32_t>(va)),
-                         "r"(static_cast<uint32_t>(va >> 32)), "r"(static_cast<uint32_t>(vq)),
-                         "r"(static_cast<uint32_t>(vq >> 32)));
-        }
+        add2(hist_lane, key[0], key[1], lo_base, add_hi[0], add_hi[1], counted[0], counted[1]);
+        add2(hist_lane, key[2], key[3], lo_base, add_hi[2], add_hi[3], counted[2], counted[3]);
     }
 
     static __device__ __forceinline__ RowTotals row_totals(const uint8_t *hist, int l, int lane) {
@@ -169,7 +177,7 @@ extern "C" int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W,
     if (B == 0) return SSB_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     auto *stats64 = reinterpret_cast<unsigned long long *>(stats);
-    int nw = 4, stg = 3;
+    int nw = 4, stg = 2;   // best of the compiled set on B200 (tools/sweep_argmax.py, SWEEP_DTYPE=f16)
     bool force_generic = false;
     if (const char *env = getenv("SSB_ARGMAX_F16_CFG")) {   // tuning knob (benchmarks only)
         if (!strcmp(env, "generic")) force_generic = true;

@@ -238,7 +238,13 @@ def test_f16_ties_and_infinities(ssb):
     h[0, :50][h[0, :50] == 0] = np.float16(-0.0)                         # mixed -0 / +0 maxima
     h[1, 10:20, :, 3] = np.float16(np.inf)
     h[1, 30:40, :, :] = np.float16(-np.inf)                              # all -inf -> label 0
-    labels, stats = check_vs_oracle(ssb, h)                              # C oracle (same fixed-point rule)
+    labels, stats = run_gpu(ssb, h)
+    o_labels, o_stats = cport.argmax_stats(h, threads=4)
+    assert (labels == o_labels).all()
+    assert (stats[..., :3] == o_stats[..., :3]).all()                    # n, Σx, Σy exact everywhere
+    assert (stats[0] == o_stats[0]).all()                                # Σq exact where winners are finite
+    finite = np.ones(19, bool); finite[[0, 3]] = False                   # frame 1: labels 0 / 3 win with -inf / +inf
+    assert (stats[1, finite, 3] == o_stats[1, finite, 3]).all()          # (infinite winners: Σq unspecified, ssb200.h)
     assert (labels[1, 10:20] == 3).all() and not labels[1, 30:40].any()
     n_labels = sp.argmax_labels(h[0])
     assert (labels[0] == n_labels).all()                                 # numpy: -0 == +0, first index wins
