@@ -82,36 +82,36 @@ struct CodecU8 {
         for (int j = 0; j < 4; ++j) key[j] = pixel_key<C>(w, j, ctx.sel);
     }
 
-    // Four 64-bit read-modify-writes of the lane-private entries of a quad's labels.
+    // 64-bit read-modify-writes of the lane-private entries of a quad's labels, two pixels at a time.
     //   add_lo = 1 | k<<24 (tile-uniform) gets q<<8 from the key; add_hi = j<<6 | dy<<16.
-    // A dependent load->add->store chain per pixel would expose ~4 x 35 cycles of shared-memory
-    // latency per warp and tile, so all four entries are loaded first; where two pixels of the quad
-    // share a label the later one adds the earlier addends itself (its load is stale) and its
-    // store, issued later to the same address, wins.
+    // Both entries of a pair are loaded first (a dependent load->add->store chain per pixel would
+    // expose the shared-memory latency four times per tile); where the two pixels share a label the
+    // second one adds the first one's addend itself (its load is stale) and its store, issued later to
+    // the same address, wins.
+    static __device__ __forceinline__ void add2(uint32_t hist_lane, uint32_t key0, uint32_t key1, uint32_t lo_base,
+                                                uint32_t hi0, uint32_t hi1, bool c0, bool c1) {
+        const uint32_t addr0 = hist_lane - __byte_perm(key0, 0u, 0x4404u);  // tag * 256
+        const uint32_t addr1 = hist_lane - __byte_perm(key1, 0u, 0x4404u);
+        const unsigned long long a0 =
+            c0 ? ((static_cast<unsigned long long>(hi0) << 32) | ((key0 & 0xff00u) | lo_base)) : 0ull;
+        const unsigned long long a1 =
+            c1 ? ((static_cast<unsigned long long>(hi1) << 32) | ((key1 & 0xff00u) | lo_base)) : 0ull;
+        uint32_t x0, x1, y0, y1;
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(x0), "=r"(x1) : "r"(addr0));
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(y0), "=r"(y1) : "r"(addr1));
+        const unsigned long long v0 = ((static_cast<unsigned long long>(x1) << 32) | x0) + a0;
+        const unsigned long long v1 =
+            ((static_cast<unsigned long long>(y1) << 32) | y0) + a1 + (addr0 == addr1 ? a0 : 0ull);
+        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr0), "r"(static_cast<uint32_t>(v0)),
+                     "r"(static_cast<uint32_t>(v0 >> 32)));
+        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr1), "r"(static_cast<uint32_t>(v1)),
+                     "r"(static_cast<uint32_t>(v1 >> 32)));
+    }
+
     static __device__ __forceinline__ void add4(uint32_t hist_lane, const uint32_t (&key)[4], uint32_t lo_base,
                                                 const uint32_t (&add_hi)[4], const bool (&counted)[4]) {
-        uint32_t addr[4];
-        unsigned long long a[4], e[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            addr[j] = hist_lane - __byte_perm(key[j], 0u, 0x4404u);  // tag * 256
-            const uint32_t add_lo = (key[j] & 0xff00u) | lo_base;
-            a[j] = counted[j] ? ((static_cast<unsigned long long>(add_hi[j]) << 32) | add_lo) : 0ull;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            uint32_t e_lo, e_hi;
-            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e_lo), "=r"(e_hi) : "r"(addr[j]));
-            e[j] = (static_cast<unsigned long long>(e_hi) << 32) | e_lo;
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            unsigned long long v = e[j] + a[j];
-#pragma unroll
-            for (int i = 0; i < j; ++i) v += addr[i] == addr[j] ? a[i] : 0ull;
-            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr[j]), "r"(static_cast<uint32_t>(v)),
-                         "r"(static_cast<uint32_t>(v >> 32)));
-        }
+        add2(hist_lane, key[0], key[1], lo_base, add_hi[0], add_hi[1], counted[0], counted[1]);
+        add2(hist_lane, key[2], key[3], lo_base, add_hi[2], add_hi[3], counted[2], counted[3]);
     }
 
     // Lane l owns label l: walk the 32 lane columns of its row (skewed start: conflict-free), adding
