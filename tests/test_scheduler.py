@@ -109,3 +109,31 @@ def test_chunked_streams_equal_single_launch():
     labels2, stats2 = sched.argmax_stats_local(q, 288, 513, chunk_frames=16, streams=streams)
     torch.cuda.synchronize()
     assert torch.equal(labels1, labels2) and torch.equal(stats1, stats2)
+
+
+@pytest.mark.gpu
+def test_concurrent_streams_share_the_scratch_pool_safely():
+    """Back-to-back calls of varying size on four streams: every call borrows a zero-at-rest scratch
+    slot; slots reused across streams are ordered with events.  All results must be exact."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    from oracle import cport
+    rng = np.random.default_rng(0)
+    streams = [torch.cuda.Stream() for _ in range(4)]
+    pending = []
+    for it in range(24):
+        b = int(rng.integers(1, 24))
+        roi = (int(rng.integers(1, 514)), 513 if it % 3 else int(rng.integers(1, 514)))
+        q = rng.integers(0, 256, (b, 513, 513, 21), dtype=np.uint8)
+        s = streams[it % 4]
+        with torch.cuda.stream(s):
+            lg = torch.from_numpy(q).cuda(non_blocking=True)
+            labels, stats = ssb200.argmax_stats(lg, roi[0], roi[1], stream=s)
+        pending.append((q, roi, labels, stats, lg))
+    torch.cuda.synchronize()
+    for q, roi, labels, stats, _ in pending:
+        want_l, want_s = cport.argmax_stats(q, roi[0], roi[1], threads=8)
+        assert (labels.cpu().numpy() == want_l).all()
+        assert (stats.cpu().numpy().view(np.uint64) == want_s).all()
