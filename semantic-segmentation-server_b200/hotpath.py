@@ -205,9 +205,12 @@ def objects_from_contours(mask, segment_img, min_area, labels):
         area = cv2.contourArea(contours[i])
         if area < min_area:
             continue
-        filled = np.zeros_like(segment_img)
-        cv2.drawContours(filled, contours, i, color=255, thickness=-1)
-        inside = segment_img[filled == 255]
+        # the reference fills a full-frame temporary per contour (sem_seg_server.py:98-103); the same
+        # pixels come out of a fill restricted to the contour's bounding box
+        bx, by, bw, bh = cv2.boundingRect(contours[i])
+        filled = np.zeros((bh, bw), dtype=np.uint8)
+        cv2.drawContours(filled, contours, i, color=255, thickness=-1, offset=(-bx, -by))
+        inside = segment_img[by:by + bh, bx:bx + bw][filled == 255]
         counts = np.bincount(inside)
         idx = int(np.argmax(counts))
         score = int(counts[idx]) / len(inside)

@@ -111,3 +111,27 @@ def test_objects_from_stats_matches_oracle(ssb):
             for g, c, w in zip(got, conf[::-1], want):
                 assert g[1:] == (w["score"], w["area"], w["cx"], w["cy"])
                 assert abs(c - w["score_conf"]) <= 1e-6 * max(1.0, abs(w["score_conf"]))
+
+
+def test_objects_from_contours_matches_reference_literal_oracle(ssb, golden):
+    """Host tail of the reference-literal path (sem_seg_server.py:88-133) on masks from the oracle:
+    identical objects to the fixtures the reference produced, and to the oracle on random scenes."""
+    import numpy as np
+    from oracle import segpath as sp
+    g = golden("objects.npz")
+    lab = golden("labels_colormap.npz")
+    names = dict(zip(lab["label_ids"].tolist(), lab["label_names"].tolist()))
+    for name in sorted(k[:-5] for k in g.files if k.endswith("_geom")):
+        W, H = (int(v) for v in g[name + "_geom"][2:4])
+        fm = g[name + "_fgmask"]
+        seg = np.ascontiguousarray(g[name + "_label_map"][:fm.shape[0], :fm.shape[1]])
+        objs = ssb.objects_from_contours(fm, seg, float(g[name + "_min_area_ratio"]) * H * W, names)
+        got = [ssb.normalise(o, W, H) for o in objs][::-1]
+        assert [o[0] for o in got] == g[name + "_obj_names"].tolist()
+        assert (np.array([o[1:] for o in got], dtype=np.float32).reshape(-1, 4) == g[name + "_obj_vals"]).all()
+    for seed in range(12):
+        lm = sp.blobby_label_map(seed, 288, 513, n_blobs=8)
+        a = [ssb.normalise(o, 513, 513) for o in ssb.objects_from_contours(sp.foreground_mask(lm), lm, 50.0, names)][::-1]
+        b = sp.reference_literal_objects(lm, 513, 513, names, 50.0 / (513 * 513))
+        assert [x[0] for x in a] == [o["label"] for o in b]
+        assert [x[1:] for x in a] == [(o["score"], o["area"], o["cx"], o["cy"]) for o in b]
