@@ -8,8 +8,9 @@
 //      11.2-byte sample stride anyway, so reading the row densely costs no extra DRAM traffic and
 //      makes the read side fully vectorised and coalesced;
 //   2. each lane gathers quads of pixels (source offsets from the host-built Pillow index table, one
-//      128-bit load per quad), swaps B and R while packing 12 bytes into three words, and stores them
-//      word-wise into a staging row;
+//      128-bit load per quad, issued while the row copy is still in flight: the kernel is bound by
+//      the chain table load -> row copy -> gather -> store of a warp, not by bytes), swaps B and R
+//      while packing 12 bytes into three words, and stores them word-wise into a staging row;
 //   3. the output row (W*3 bytes, 1539 B: its 16-byte phase changes from row to row) leaves as
 //      128-bit global stores; the staging row is re-aligned to that phase on the way out with funnel
 //      shifts (byte stores only for the ragged head and tail).
@@ -23,6 +24,7 @@ namespace ssb {
 namespace {
 
 constexpr int kPreWarps = 4, kPreThreads = kPreWarps * 32;
+constexpr int kPrePrefetch = 5;   // quads per lane whose table entries are prefetched: 5 * 32 * 4 >= 513 columns
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
@@ -67,16 +69,22 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
     for (int i = lane; i < head; i += 32) sp[i] = srow[i];
     for (int i = lane; i < body16; i += 32) cp_async16(sp + head + i * 16, srow + head + i * 16);
     for (int i = head + body16 * 16 + lane; i < row_bytes; i += 32) sp[i] = srow[i];
+    // the index-table entries of this lane's first quads are fetched while the row is in flight
+    const int quads = (W + 3) >> 2;
+    int4 pre[kPrePrefetch];
+#pragma unroll
+    for (int k = 0; k < kPrePrefetch; ++k) {
+        const int x0 = (lane + 32 * k) * 4;
+        pre[k] = x0 + 3 < new_w ? *reinterpret_cast<const int4 *>(xtab + x0) : make_int4(0, 0, 0, 0);   // 16-byte aligned table
+    }
     cp_async_wait_all();
     __syncwarp();
 
     // 2. gather: quads of output pixels -> three packed words each
-    const int quads = (W + 3) >> 2;
-    for (int q = lane; q < quads; q += 32) {
+    auto do_quad = [&](int q, const int4 &t) {
         const int x0 = q * 4;
         int xs[4];
         if (x0 + 3 < new_w) {
-            const int4 t = *reinterpret_cast<const int4 *>(xtab + x0);   // table is 16-byte aligned (x0 % 4 == 0)
             xs[0] = t.x; xs[1] = t.y; xs[2] = t.z; xs[3] = t.w;
         } else {
 #pragma unroll
@@ -96,6 +104,13 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
         dst[3 * q + 0] = px[0] | (px[1] << 24);
         dst[3 * q + 1] = (px[1] >> 8) | (px[2] << 16);
         dst[3 * q + 2] = (px[2] >> 16) | (px[3] << 8);
+    };
+#pragma unroll
+    for (int k = 0; k < kPrePrefetch; ++k)
+        if (lane + 32 * k < quads) do_quad(lane + 32 * k, pre[k]);
+    for (int q = lane + 32 * kPrePrefetch; q < quads; q += 32) {   // model inputs wider than 640 columns
+        const int x0 = q * 4;
+        do_quad(q, x0 + 3 < new_w ? *reinterpret_cast<const int4 *>(xtab + x0) : make_int4(0, 0, 0, 0));
     }
     __syncwarp();
 
