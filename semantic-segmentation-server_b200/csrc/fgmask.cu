@@ -21,6 +21,7 @@ __device__ __forceinline__ int reflect101(int i, int n) {
 // of 9 + 9.  The colour LUT packs channel 0/1 into 16-bit fields of one word (box sums <= 9*255 fit)
 // and channel 2 into a second word, so a box sum is 2 integer adds per neighbour.
 constexpr int kMaskPxPerThread = 4, kMaskTileW = 32 * kMaskPxPerThread, kMaskTileH = 8;
+constexpr int kMaskTilesPerCta = 8;   // vertical tiles per CTA: the LUT set-up (global loads + barrier) is paid once per 64 rows
 
 __global__ void __launch_bounds__(256)
 fg_mask_kernel(const uint8_t *__restrict__ labels, int H, int W, int roi_h, int roi_w,
@@ -32,13 +33,15 @@ fg_mask_kernel(const uint8_t *__restrict__ labels, int H, int W, int roi_h, int 
         cmap[i] = make_uint2(colormap[3 * i] | (colormap[3 * i + 1] << 16), colormap[3 * i + 2]);
     __syncthreads();
     const int x0 = blockIdx.x * kMaskTileW + (threadIdx.x & 31) * kMaskPxPerThread;
-    const int y = blockIdx.y * kMaskTileH + (threadIdx.x >> 5);
-    if (x0 >= W || y >= H) return;
+    if (x0 >= W) return;
+    for (int ty = 0; ty < kMaskTilesPerCta; ++ty) {
+    const int y = (blockIdx.y * kMaskTilesPerCta + ty) * kMaskTileH + (threadIdx.x >> 5);
+    if (y >= H) return;
     uint8_t *out = mask + static_cast<long long>(blockIdx.z) * H * W + static_cast<long long>(y) * W + x0;
     const int n_out = min(kMaskPxPerThread, W - x0);
     if (y >= roi_h || x0 >= roi_w) {
         for (int j = 0; j < n_out; ++j) out[j] = 0;
-        return;
+        continue;
     }
     const uint8_t *frame = labels + static_cast<long long>(blockIdx.z) * H * W;
     const uint8_t *rows[3] = {frame + static_cast<long long>(reflect101(y - 1, roi_h)) * W,
@@ -70,6 +73,7 @@ fg_mask_kernel(const uint8_t *__restrict__ labels, int H, int W, int roi_h, int 
         }
         out[j] = m;
     }
+    }
 }
 
 }  // namespace
@@ -84,7 +88,7 @@ extern "C" int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int ro
     if (B == 0) return SSB_OK;
     if (!labels || !colormap || !mask) return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
     if (B > 65535 || (H + 7) / 8 > 65535) return fail(SSB_ERR_LIMIT, "B and H/8 must be <= 65535");
-    dim3 grid((W + kMaskTileW - 1) / kMaskTileW, (H + kMaskTileH - 1) / kMaskTileH, B);
+    dim3 grid((W + kMaskTileW - 1) / kMaskTileW, (H + kMaskTileH * kMaskTilesPerCta - 1) / (kMaskTileH * kMaskTilesPerCta), B);
     SSB_CUDA_TRY(launch_pdl(fg_mask_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream), labels, H, W, roi_h,
                             roi_w, colormap, mask));
     return SSB_OK;
