@@ -66,6 +66,16 @@ class ArrayCamera:
         return {cv2.CAP_PROP_FRAME_WIDTH: w, cv2.CAP_PROP_FRAME_HEIGHT: h}.get(prop, 0)
 
 
+_pool = None
+
+
+def _contour_pool():
+    global _pool
+    if _pool is None:
+        _pool = concurrent.futures.ThreadPoolExecutor(max_workers=min(8, len(os.sched_getaffinity(0))))
+    return _pool
+
+
 def _open_camera(camera_idx):
     if hasattr(camera_idx, "read"):
         return camera_idx
@@ -108,13 +118,17 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
                 labels_h = label_maps[:, :geom.roi_h, :geom.roi_w].cpu().numpy()
             else:
                 stats_h = stats.cpu().numpy()
-            for i in range(len(frames)):
-                if mode == "contours":
-                    objs = hotpath.objects_from_contours(masks_h[i], labels_h[i], segment_centroid_min_area, labels)
-                else:
-                    objs, _ = hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, scale,
-                                                         zero_point, fixed_shift=0 if logits.dtype == torch.uint8
-                                                         else hotpath._cabi.F16_FIXED_SHIFT)
+            if mode == "contours":
+                # OpenCV releases the GIL: the per-frame contour tails of a batch run side by side;
+                # results are consumed in frame order, so the deque looks exactly as in the reference
+                per_frame = list(_contour_pool().map(
+                    lambda i: hotpath.objects_from_contours(masks_h[i], labels_h[i], segment_centroid_min_area, labels),
+                    range(len(frames))))
+            else:
+                shift = 0 if logits.dtype == torch.uint8 else hotpath._cabi.F16_FIXED_SHIFT
+                per_frame = [hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, scale,
+                                                        zero_point, fixed_shift=shift)[0] for i in range(len(frames))]
+            for objs in per_frame:
                 for o in objs:
                     lab, score, area, cx, cy = hotpath.normalise(o, width, height)  # :184-192
                     segmented_objects.appendleft(proto.SegmentedObject(
