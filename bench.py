@@ -182,6 +182,20 @@ def other_kernels(ssb200, torch):
     us = _time_us(torch, lambda i: ssb200.foreground_mask(labels, ROI_H, ROI_W, cm, out=mask), 20)
     out.append({"kernel": "fg_mask (513x513, batch 64)", "us": us, "frames_per_s": b / us * 1e6,
                 "GBps": 2 * H * W * b / us / 1e3})
+    # same kernel on "blobby" label maps (long same-label runs, ~70 % background: SURVEY set U1) -- the
+    # lane-private histograms make the statistics independent of the label distribution
+    field = torch.randint(1, C, (b, 33, 33), device="cuda", generator=g)
+    field[torch.rand((b, 33, 33), device="cuda", generator=g) < 0.7] = 0
+    lab_true = field.repeat_interleave(16, 1).repeat_interleave(16, 2)[:, :H, :W]
+    qb = torch.randint(0, 180, (b, H, W, C), dtype=torch.uint8, device="cuda", generator=g)
+    qb.scatter_(3, lab_true.unsqueeze(-1), torch.randint(200, 256, (b, H, W, 1), dtype=torch.uint8, device="cuda", generator=g))
+    lab_b = torch.empty((b, H, W), dtype=torch.uint8, device="cuda")
+    st_b = torch.empty((b, C, 4), dtype=torch.int64, device="cuda")
+    us = _time_us(torch, lambda i: ssb200.argmax_stats(qb, ROI_H, ROI_W, labels=lab_b, stats=st_b), 40)
+    assert bool((lab_b.long() == lab_true).all())
+    out.append({"kernel": "argmax_stats u8, blobby label maps (batch 64, one batch re-read: L2 holds 1/3 of it)", "us": us,
+                "frames_per_s": b / us * 1e6, "GBps": ALGO_BYTES_PER_FRAME * b / us / 1e3})
+    del qb, field, lab_true
     # config 1: one frame, K1 -> K2+K3, launch to completion (latency; the data is L2-resident)
     f1 = torch.randint(0, 256, (1, H, W, 3), dtype=torch.uint8, device="cuda", generator=g)
     g1 = ssb200.FrameGeometry(W, H, H, W)
