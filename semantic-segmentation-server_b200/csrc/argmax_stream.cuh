@@ -251,7 +251,8 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_stream_kernel(
         }
 
         // statistics.  Tile classes (CTA-uniform): interior = one frame, every pixel inside the ROI
-        // (no per-pixel tests); exterior = one frame, every pixel outside; mixed = the rest.
+        // (no per-pixel tests); exterior = one frame, every row below the ROI; border = one frame,
+        // per-pixel ROI tests; the rest = tiles that straddle two frames.
         const bool one_frame = r0 + K::kTilePx <= p.hw;
         const uint32_t y_first = fastdiv(static_cast<uint32_t>(r0), p.divw);
         const uint32_t y_last = fastdiv(static_cast<uint32_t>(r0 + K::kTilePx - 1), p.divw);
@@ -268,8 +269,26 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_stream_kernel(
                 add_hi[j] = hi_base + (j << (kFieldJ - 32)) + (static_cast<uint32_t>(j) >= d ? 1u << (kFieldDy - 32) : 0u);
             const bool all[4] = {true, true, true, true};
             Codec::add4(hist_lane, key, lo_base, add_hi, all);
-        } else if (one_frame && p.roi_w == p.w && y_first >= static_cast<uint32_t>(p.roi_h)) {
+        } else if (one_frame && y_first >= static_cast<uint32_t>(p.roi_h)) {
             covered += K::kTilePx;  // padding rows below the ROI: labels only
+        } else if (one_frame) {
+            // the ROI border runs through the tile (or roi_w < W): per-pixel tests, coordinates stepped
+            // from the quad's first pixel (W >= 4: at most one row wrap inside a quad)
+            covered += K::kTilePx;
+            const uint32_t rq = static_cast<uint32_t>(r0 + i0);
+            const uint32_t yq = fastdiv(rq, p.divw);
+            const uint32_t xq = rq - yq * p.w;
+            const uint32_t lo_base = 1u | (static_cast<uint32_t>(k) << kFieldK);
+            uint32_t add_hi[4];
+            bool counted[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool wrap = xq + j >= static_cast<uint32_t>(p.w);
+                const uint32_t x = xq + j - (wrap ? p.w : 0), y = yq + (wrap ? 1u : 0u);
+                counted[j] = (x < static_cast<uint32_t>(p.roi_w)) & (y < static_cast<uint32_t>(p.roi_h));
+                add_hi[j] = (j << (kFieldJ - 32)) | ((y - y_base) << (kFieldDy - 32));
+            }
+            Codec::add4(hist_lane, key, lo_base, add_hi, counted);
         } else {
             int lo = 0;  // one segment per frame the tile touches
             while (true) {
