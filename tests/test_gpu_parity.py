@@ -98,6 +98,16 @@ def test_u8_shapes(ssb, shape):
     check_vs_oracle(ssb, q, max(1, shape[1] // 2), max(1, shape[2] - 1))
 
 
+@pytest.mark.parametrize("shape", [(200, 8, 8, 21), (64, 3, 4, 21), (7, 4000, 4, 19), (5, 1, 3000, 21),
+                                   (1000, 5, 5, 19), (3, 2, 1025, 21)])
+def test_u8_extreme_geometries_on_the_streaming_path(ssb, shape):
+    """Frames much smaller than a tile (many frame changes inside one tile), very narrow and very wide
+    rows: the flat-stream kernel's frame bookkeeping and packed row counters."""
+    q = np.random.default_rng(sum(shape)).integers(0, 256, shape, dtype=np.uint8)
+    check_vs_oracle(ssb, q)
+    check_vs_oracle(ssb, q, max(1, shape[1] - 1), max(1, shape[2] // 2))
+
+
 def test_u8_narrow_value_range_many_ties(ssb):
     q = np.random.default_rng(5).integers(0, 3, (2, 513, 513, 21), dtype=np.uint8)
     check_vs_oracle(ssb, q)
