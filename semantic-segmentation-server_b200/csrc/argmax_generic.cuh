@@ -46,6 +46,20 @@ argmax_stats_generic_kernel(const typename E::T *logits, uint8_t *labels, unsign
     __syncthreads();
     const long long f = blockIdx.y;
     const int r_begin = blockIdx.x * chunk_px, r_end = min(hw, r_begin + chunk_px);
+    // Each thread keeps the sums of its current label in registers and only touches the block
+    // accumulators when the label changes: segmentation maps have long same-label runs, and a thread's
+    // consecutive pixels (256 apart, usually the same row) mostly share a label.
+    int cur = -1;
+    unsigned long long cn = 0, cx = 0, cy = 0, cq = 0;
+    auto spill = [&]() {
+        if (cn) {
+            atomicAdd(&blk[cur * 4 + SSB_STAT_N], cn);
+            atomicAdd(&blk[cur * 4 + SSB_STAT_SX], cx);
+            atomicAdd(&blk[cur * 4 + SSB_STAT_SY], cy);
+            atomicAdd(&blk[cur * 4 + SSB_STAT_SQ], cq);
+        }
+        cn = cx = cy = cq = 0;
+    };
     for (int r = r_begin + threadIdx.x; r < r_end; r += kGenericThreads) {
         const typename E::T *q = logits + (f * hw + r) * C;
         int best = 0;
@@ -57,12 +71,17 @@ argmax_stats_generic_kernel(const typename E::T *logits, uint8_t *labels, unsign
         if (labels) labels[f * hw + r] = static_cast<uint8_t>(best);
         const int y = r / w, x = r - y * w;
         if (x < roi_w && y < roi_h) {
-            atomicAdd(&blk[best * 4 + SSB_STAT_N], 1ull);
-            atomicAdd(&blk[best * 4 + SSB_STAT_SX], static_cast<unsigned long long>(x));
-            atomicAdd(&blk[best * 4 + SSB_STAT_SY], static_cast<unsigned long long>(y));
-            atomicAdd(&blk[best * 4 + SSB_STAT_SQ], E::fixed(q + best));
+            if (best != cur) {
+                spill();
+                cur = best;
+            }
+            cn += 1;
+            cx += static_cast<unsigned long long>(x);
+            cy += static_cast<unsigned long long>(y);
+            cq += E::fixed(q + best);
         }
     }
+    spill();
     __syncthreads();
     for (int i = threadIdx.x; i < C * 4; i += kGenericThreads) {
         const unsigned long long v = blk[i];
