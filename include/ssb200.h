@@ -102,6 +102,21 @@ SSB_API int ssb_argmax_stats_u8(const uint8_t *logits, int B, int H, int W, int 
 SSB_API int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
                          uint8_t *labels, uint64_t *stats, void *stream);
 
+/* Planar class scores, [B][C][H][W] ("NCHW"): what a convolutional segmentation head leaves on the
+ * GPU when it stands in for the Edge TPU call of sem_seg_server.py:162 (torchvision's
+ * DeepLabv3 returns fp32, fp16 under autocast).  Outputs, ROI, limits and tie rule are those of
+ * ssb_argmax_stats_u8; inputs must be NaN-free.
+ *   _f32: SQ accumulates round-to-nearest-even(value * 2^24) as a two's-complement int64: exact for
+ *         values that are multiples of 2^-24 (all fp16-representable ones), otherwise within 2^-25 per
+ *         pixel of the real sum; |value| < 2^39.
+ *   _f16: 16-bit halves as uint16_t bit patterns; SQ = sum of value * 2^24, exact (finite winners).
+ * `logits` needs element alignment only (fp16 loads pixel pairs when it is 4-byte aligned); `labels`
+ * may have any alignment.  C = 19 and 21 run the unrolled kernel, other class counts a generic one. */
+SSB_API int ssb_argmax_stats_nchw_f32(const float *logits, int B, int H, int W, int C, int roi_h, int roi_w,
+                              uint8_t *labels, uint64_t *stats, void *stream);
+SSB_API int ssb_argmax_stats_nchw_f16(const uint16_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
+                              uint8_t *labels, uint64_t *stats, void *stream);
+
 /* No counterpart in the reference: an extra way to call the u8 argmax + statistics pass for hosts
  * that must not trigger a device allocation.
  *

@@ -116,12 +116,15 @@ def argmax_labels(logits):
 
 
 def winning_logit_fixed(logits, labels):
-    """Exact integer value of the winning logit: raw q for u8, value*2**24 for fp16."""
+    """Integer value of the winning logit: raw q for u8, value*2**24 for fp16 (exact), the same
+    rounded half-to-even for fp32 (the planar entry points' contract, include/ssb200.h)."""
     win = np.take_along_axis(logits, labels[..., None].astype(np.int64), axis=-1)[..., 0]
     if logits.dtype == np.uint8:
         return win.astype(np.int64)
     if logits.dtype == np.float16:
         return np.ldexp(win.astype(np.float64), F16_FIXED_SHIFT).astype(np.int64)
+    if logits.dtype == np.float32:
+        return np.rint(np.ldexp(win.astype(np.float64), F16_FIXED_SHIFT)).astype(np.int64)
     raise TypeError(logits.dtype)
 
 
@@ -157,6 +160,11 @@ def argmax_stats(logits, roi_h=None, roi_w=None):
         labels[i] = argmax_labels(logits[i])
         stats[i] = label_stats(labels[i], winning_logit_fixed(logits[i], labels[i]), c, roi_h, roi_w)
     return labels, stats
+
+
+def argmax_stats_nchw(logits, roi_h=None, roi_w=None):
+    """Oracle for ssb_argmax_stats_nchw_{f32,f16}: planar [B,C,H,W] scores, same outputs."""
+    return argmax_stats(np.ascontiguousarray(np.transpose(logits, (0, 2, 3, 1))), roi_h, roi_w)
 
 
 # --------------------------------------------------------------------------------------

@@ -26,6 +26,10 @@ SIGNATURES = {
                                              _c_void_p, _c_void_p, _c_void_p]),
     "ssb_argmax_stats_f16": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
                                       _c_void_p, _c_void_p, _c_void_p]),
+    "ssb_argmax_stats_nchw_f32": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
+                                           _c_void_p, _c_void_p, _c_void_p]),
+    "ssb_argmax_stats_nchw_f16": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
+                                           _c_void_p, _c_void_p, _c_void_p]),
     "ssb_fg_mask_u8": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p,
                                 _c_void_p]),
     "ssb_pipeline_create": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),

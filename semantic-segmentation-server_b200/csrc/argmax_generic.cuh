@@ -1,7 +1,9 @@
 // Generic (any C, any alignment) argmax + per-label statistics kernel.  Correct for every shape the
 // C-ABI accepts; used when the streaming fast path does not apply (C not compiled in, misaligned
 // views, tiny frames).  One CTA handles a chunk of ONE frame: scalar loads, block accumulators in
-// shared memory via 64-bit atomics, one global flush per block.
+// shared memory via 64-bit atomics, one global flush per block.  The element of pixel r, channel c
+// of a frame sits at r*px_stride + c*ch_stride: (C, 1) for [H,W,C] frames, (1, H*W) for planar
+// [C,H,W] frames (argmax_planar.cu).
 #pragma once
 #include <cuda_fp16.h>
 
@@ -34,13 +36,25 @@ struct ElemF16 {
     }
 };
 
+// fp32 scores: Σq adds round-to-nearest-even(value * 2^24) (exact whenever the value is a multiple
+// of 2^-24, e.g. every fp16-representable value; |value| < 2^39 keeps it inside an int64).
+struct ElemF32 {
+    using T = float;
+    using V = float;
+    static __device__ __forceinline__ V load(const T *p) { return *p; }
+    static __device__ __forceinline__ bool gt(V a, V b) { return a > b; }
+    static __device__ __forceinline__ unsigned long long fixed(const T *p) {
+        return static_cast<unsigned long long>(__float2ll_rn(*p * 16777216.0f));
+    }
+};
+
 constexpr int kGenericThreads = 256;
 constexpr int kGenericMaxC = 255;
 
 template <typename E>
 __global__ void __launch_bounds__(kGenericThreads)
 argmax_stats_generic_kernel(const typename E::T *logits, uint8_t *labels, unsigned long long *stats, int hw, int w,
-                            int C, int roi_h, int roi_w, int chunk_px) {
+                            int C, int roi_h, int roi_w, int chunk_px, long long px_stride, long long ch_stride) {
     __shared__ unsigned long long blk[kGenericMaxC * 4];
     for (int i = threadIdx.x; i < C * 4; i += kGenericThreads) blk[i] = 0ull;
     __syncthreads();
@@ -61,11 +75,11 @@ argmax_stats_generic_kernel(const typename E::T *logits, uint8_t *labels, unsign
         cn = cx = cy = cq = 0;
     };
     for (int r = r_begin + threadIdx.x; r < r_end; r += kGenericThreads) {
-        const typename E::T *q = logits + (f * hw + r) * C;
+        const typename E::T *q = logits + f * hw * C + r * px_stride;
         int best = 0;
         typename E::V bv = E::load(q);
         for (int c = 1; c < C; ++c) {
-            const typename E::V v = E::load(q + c);
+            const typename E::V v = E::load(q + c * ch_stride);
             if (E::gt(v, bv)) { bv = v; best = c; }
         }
         if (labels) labels[f * hw + r] = static_cast<uint8_t>(best);
@@ -78,7 +92,7 @@ argmax_stats_generic_kernel(const typename E::T *logits, uint8_t *labels, unsign
             cn += 1;
             cx += static_cast<unsigned long long>(x);
             cy += static_cast<unsigned long long>(y);
-            cq += E::fixed(q + best);
+            cq += E::fixed(q + best * ch_stride);
         }
     }
     spill();
@@ -91,8 +105,9 @@ argmax_stats_generic_kernel(const typename E::T *logits, uint8_t *labels, unsign
 
 template <typename E>
 inline int launch_generic(const typename E::T *logits, int B, int H, int W, int C, int roi_h, int roi_w,
-                          uint8_t *labels, unsigned long long *stats, cudaStream_t st) {
+                          uint8_t *labels, unsigned long long *stats, cudaStream_t st, bool planar = false) {
     const int hw = H * W;
+    const long long px_stride = planar ? 1 : C, ch_stride = planar ? hw : 1;
     const int chunk_px = 8192;
     dim3 grid((hw + chunk_px - 1) / chunk_px, 1);
     // gridDim.y is limited to 65535: launch in slabs of frames
@@ -100,7 +115,7 @@ inline int launch_generic(const typename E::T *logits, int B, int H, int W, int 
         grid.y = min(65535, B - b0);
         argmax_stats_generic_kernel<E><<<grid, kGenericThreads, 0, st>>>(
             logits + static_cast<long long>(b0) * hw * C, labels ? labels + static_cast<long long>(b0) * hw : nullptr,
-            stats + static_cast<long long>(b0) * C * 4, hw, W, C, roi_h, roi_w, chunk_px);
+            stats + static_cast<long long>(b0) * C * 4, hw, W, C, roi_h, roi_w, chunk_px, px_stride, ch_stride);
         SSB_CUDA_TRY(cudaGetLastError());
     }
     return SSB_OK;

@@ -196,21 +196,27 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_stream_kernel(
         __syncwarp();
     };
 
+    // a [C][4] block has more entries than a 2-warp CTA has consumer threads: 1 round for NWARPS >= 4
+    constexpr int kEntryIters = (C * 4 + K::kConsumers - 1) / K::kConsumers;
     // All consumer threads: add this CTA's share of frame f to scratch, then report `covered` pixels.
     // The CTA whose report completes the frame publishes it and leaves scratch zero again.
     auto frame_flush = [&]() {
         if (covered == 0) return;  // CTA-uniform: nothing accumulated for f
         warp_flush();
         named_bar_sync(1, K::kConsumers);
-        if (tid < C * 4) {
-            unsigned long long v = 0ull;
 #pragma unroll
-            for (int wi = 0; wi < NWARPS; ++wi) {
-                v += blk[wi * C * 4 + tid];
-                blk[wi * C * 4 + tid] = 0ull;
+        for (int it = 0; it < kEntryIters; ++it) {
+            const int e = tid + it * K::kConsumers;
+            if (e < C * 4) {
+                unsigned long long v = 0ull;
+#pragma unroll
+                for (int wi = 0; wi < NWARPS; ++wi) {
+                    v += blk[wi * C * 4 + e];
+                    blk[wi * C * 4 + e] = 0ull;
+                }
+                if (v) atomicAdd(&p.acc[f * (C * 4) + e], v);
+                __threadfence();
             }
-            if (v) atomicAdd(&p.acc[f * (C * 4) + tid], v);
-            __threadfence();
         }
         named_bar_sync(1, K::kConsumers);
         if (tid == 0) {
@@ -220,7 +226,11 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_stream_kernel(
         }
         named_bar_sync(1, K::kConsumers);
         if (s_last) {
-            if (tid < C * 4) p.stats[f * (C * 4) + tid] = atomicExch(&p.acc[f * (C * 4) + tid], 0ull);
+#pragma unroll
+            for (int it = 0; it < kEntryIters; ++it) {
+                const int e = tid + it * K::kConsumers;
+                if (e < C * 4) p.stats[f * (C * 4) + e] = atomicExch(&p.acc[f * (C * 4) + e], 0ull);
+            }
             if (tid == 0) p.frame_px[f] = 0u;
         }
         covered = 0;

@@ -155,6 +155,30 @@ def argmax_stats(logits, roi_h=None, roi_w=None, labels=None, stats=None, want_l
     return (labels if want_labels else None), stats
 
 
+def argmax_stats_nchw(logits, roi_h=None, roi_w=None, labels=None, stats=None, want_labels=True, stream=None):
+    """[B,C,H,W] fp32 or fp16 class scores (device, contiguous) -> (labels [B,H,W] u8 | None, stats
+    [B,C,4] int64): argmax_stats for the planar layout a convolutional head leaves on the GPU when it
+    replaces engine.run_inference (sem_seg_server.py:162).  The fourth statistic is the sum of
+    round(score * 2**24) (fixed_shift=_cabi.F16_FIXED_SHIFT in objects_from_stats)."""
+    _require_cuda(logits, "logits")
+    if logits.dim() != 4 or logits.dtype not in (torch.float32, torch.float16) or not logits.is_contiguous():
+        raise ValueError("logits must be a contiguous [B,C,H,W] float32 or float16 tensor")
+    b, c, h, w = logits.shape
+    roi_h = h if roi_h is None else roi_h
+    roi_w = w if roi_w is None else roi_w
+    dev = logits.device
+    if want_labels and labels is None:
+        labels = torch.empty((b, h, w), dtype=torch.uint8, device=dev)
+    if stats is None:
+        stats = torch.empty((b, c, 4), dtype=torch.int64, device=dev)
+    _require_cuda(stats, "stats")
+    fn = _cabi.lib.ssb_argmax_stats_nchw_f32 if logits.dtype == torch.float32 else _cabi.lib.ssb_argmax_stats_nchw_f16
+    with torch.cuda.device(dev):
+        _cabi.check(fn(logits.data_ptr(), b, h, w, c, roi_h, roi_w,
+                       labels.data_ptr() if want_labels else None, stats.data_ptr(), _stream_ptr(stream)))
+    return (labels if want_labels else None), stats
+
+
 def foreground_mask(labels, roi_h, roi_w, colormap_dev=None, out=None, stream=None):
     """[B,H,W] u8 label maps (device) -> [B,H,W] u8 mask, 255 where the reference's
     blur/gray/threshold stage (sem_seg_server.py:173,79-85) is foreground inside the ROI."""

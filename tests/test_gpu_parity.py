@@ -29,7 +29,10 @@ def digest(a):
 
 def run_gpu(ssb, logits_np, roi_h=None, roi_w=None, want_labels=True):
     lg = torch.from_numpy(logits_np).cuda()
-    labels, stats = ssb.argmax_stats(lg, roi_h, roi_w, want_labels=want_labels)
+    # poisoned output: torch.empty hands back the block of the previous call, which would hide an entry
+    # the kernel forgot to write
+    stats = torch.full((lg.shape[0], lg.shape[3], 4), -0x5A5A5A5A, dtype=torch.int64, device="cuda")
+    labels, stats = ssb.argmax_stats(lg, roi_h, roi_w, stats=stats, want_labels=want_labels)
     torch.cuda.synchronize()
     return (labels.cpu().numpy() if want_labels else None), stats.cpu().numpy().view(np.uint64)
 
