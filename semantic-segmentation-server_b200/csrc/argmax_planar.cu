@@ -136,18 +136,30 @@ __device__ __forceinline__ PlanarTotals planar_row_totals(const uint8_t *hist, i
 }
 
 // ---- per-tile argmax ------------------------------------------------------------------------------
+// pc + plane_bytes, opaque to the optimiser: left to itself it keeps a base and a running offset and
+// spends four integer instructions per plane on addresses where two suffice.
+__device__ __forceinline__ const char *next_plane(const char *pc, long long plane_bytes) {
+    unsigned long long a = reinterpret_cast<unsigned long long>(pc);
+    asm("add.u64 %0, %0, %1;" : "+l"(a) : "l"(plane_bytes));
+    return reinterpret_cast<const char *>(a);
+}
+
 // One load per score.  `lgw` points at plane 0 of the warp's 128-pixel chunk; pixels at or beyond
 // `n_chunk` (pixels of the chunk inside the frame) are not loaded.
 template <typename P, int C, bool FULL>
 __device__ __forceinline__ void classify_scalar(const typename P::Elem::T *lgw, long long hw, int lane, int n_chunk,
                                                 uint32_t (&best)[4], uint32_t (&lab)[4]) {
+    // one running BYTE pointer per thread (a 64-bit add per plane); everything else is an immediate
+    const char *pc = reinterpret_cast<const char *>(lgw + P::kLane * lane);
+    const long long plane_bytes = hw * P::kBytes;
 #pragma unroll
-    for (int c = 0; c < C; ++c) {
+    for (int c = 0; c < C; ++c, pc = next_plane(pc, plane_bytes)) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int off = pixel_offset<P>(j, lane);
             uint32_t v = 0u;
-            if (FULL || off < n_chunk) v = P::ldg(lgw + c * hw + off);
+            if (FULL || off < n_chunk)
+                v = P::ldg(reinterpret_cast<const typename P::Elem::T *>(pc) + (P::kA * P::field_a(j) + P::field_b(j)));
             if (c == 0) {
                 best[j] = v;
                 lab[j] = 0u;
@@ -173,14 +185,17 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
                                                uint32_t (&lab)[4]) {
     uint32_t bA[2], lA[2], bB[2], lB[2], bX = 0u, lX = 0u;
     bool haveA = false, haveB = false;
+    const char *pc = reinterpret_cast<const char *>(lgw + 2 * lane);   // running byte pointer, see classify_scalar
+    const long long plane_bytes = hw * 2;
 #pragma unroll
-    for (int c = 0; c < C; ++c) {
+    for (int c = 0; c < C; ++c, pc = next_plane(pc, plane_bytes)) {
+        const uint16_t *q = reinterpret_cast<const uint16_t *>(pc);
         const bool aligned = MODE == 0 || ((c & 1) == (MODE == 1 ? 0 : 1));
         const uint32_t cc = static_cast<uint32_t>(c) * 0x00010001u;
         if (aligned) {
 #pragma unroll
             for (int jj = 0; jj < 2; ++jj) {
-                const uint32_t v = __ldg(reinterpret_cast<const unsigned int *>(lgw + c * hw + 64 * jj + 2 * lane));
+                const uint32_t v = __ldg(reinterpret_cast<const unsigned int *>(q + 64 * jj));
                 if (!haveA) {
                     bA[jj] = v;
                     lA[jj] = cc;
@@ -194,7 +209,7 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
         } else {
 #pragma unroll
             for (int jj = 0; jj < 2; ++jj) {
-                const uint32_t v = __ldg(reinterpret_cast<const unsigned int *>(lgw + c * hw + 64 * jj + 2 * lane - 1));
+                const uint32_t v = __ldg(reinterpret_cast<const unsigned int *>(q + 64 * jj - 1));
                 if (!haveB) {
                     bB[jj] = v;
                     lB[jj] = cc;
@@ -206,7 +221,7 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
             }
             // pixel 127 of the chunk is in none of the shifted words: lane 31 tracks it on its own
             uint32_t x = 0u;
-            if (lane == 31) x = __ldg(lgw + c * hw + 127);
+            if (lane == 31) x = __ldg(q + 65);   // pixel 127: q already holds 2*31
             if (!haveB) {
                 bX = x;
                 lX = static_cast<uint32_t>(c);
@@ -388,8 +403,21 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
             }
         }
 
-        // statistics (tiles whose rows all lie below the ROI contribute labels only)
-        if (fastdiv(static_cast<uint32_t>(r0), p.divw) < static_cast<uint32_t>(p.roi_h)) {
+        // statistics.  Tile classes (CTA-uniform): interior = full tile, every pixel inside the ROI (no
+        // per-pixel tests); tiles whose rows all lie below the ROI contribute labels only; the rest test
+        // every pixel.
+        if (n_valid == kTilePx && p.roi_w == p.w &&
+            fastdiv(static_cast<uint32_t>(r0 + kTilePx - 1), p.divw) < static_cast<uint32_t>(p.roi_h)) {
+            uint32_t add_lo[4], add_hi[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t y = fastdiv(static_cast<uint32_t>(r0 + 128 * warp + pixel_offset<P>(j, lane)), p.divw);
+                add_lo[j] = 1u | (static_cast<uint32_t>(P::field_b(j)) << kFieldB) | (static_cast<uint32_t>(k) << kFieldK);
+                add_hi[j] = (static_cast<uint32_t>(P::field_a(j)) << (kFieldJ - 32)) | ((y - y_base) << (kFieldDy - 32));
+            }
+            planar_add2<P>(hist_lane, lab[0], lab[1], best[0], best[1], add_lo[0], add_lo[1], add_hi[0], add_hi[1], true, true);
+            planar_add2<P>(hist_lane, lab[2], lab[3], best[2], best[3], add_lo[2], add_lo[3], add_hi[2], add_hi[3], true, true);
+        } else if (fastdiv(static_cast<uint32_t>(r0), p.divw) < static_cast<uint32_t>(p.roi_h)) {
             uint32_t add_lo[4], add_hi[4];
             bool counted[4];
 #pragma unroll
