@@ -207,6 +207,17 @@ def other_kernels(ssb200, torch):
     out.append({"kernel": "argmax_stats u8, blobby label maps (batch 64, one batch re-read: L2 holds 1/3 of it)", "us": us,
                 "frames_per_s": b / us * 1e6, "GBps": ALGO_BYTES_PER_FRAME * b / us / 1e3})
     del qb, field, lab_true
+    # planar scores left on the GPU by a convolutional head (row f4): fp32 and fp16 [B,21,513,513]
+    for dt, nb in ((torch.float32, 32), (torch.float16, 64)):
+        pl = [torch.randn((nb, C, H, W), dtype=dt, device="cuda", generator=g) for _ in range(2)]
+        lab_p = torch.empty((nb, H, W), dtype=torch.uint8, device="cuda")
+        st_p = torch.empty((nb, C, 4), dtype=torch.int64, device="cuda")
+        us = _time_us(torch, lambda i: ssb200.argmax_stats_nchw(pl[i % 2], labels=lab_p, stats=st_p), 40)
+        algo = (H * W * C * pl[0].element_size() + H * W + C * 32) * nb
+        out.append({"kernel": "argmax_stats_nchw %s (21x513x513 planar, batch %d)" % ("fp32" if dt == torch.float32 else "fp16", nb),
+                    "us": us, "frames_per_s": nb / us * 1e6, "GBps": algo / us / 1e3,
+                    "frac_of_measured_peak": algo / us / 1e3 / peak})
+        del pl
     # config 1: one frame, K1 -> K2+K3, launch to completion (latency; the data is L2-resident)
     f1 = torch.randint(0, 256, (1, H, W, 3), dtype=torch.uint8, device="cuda", generator=g)
     g1 = ssb200.FrameGeometry(W, H, H, W)

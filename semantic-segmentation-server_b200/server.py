@@ -6,9 +6,10 @@ reply semantics, with the per-frame path running on the GPU in batches.
     serve                   :236-291                    flags, engine/labels/camera set-up, gRPC lifecycle
 
 The model (`engine`) is a duck type, as in the reference: `get_input_tensor_shape()` -> (1,H,W,3) and
-`run_logits(input_u8 [B,H,W,3] cuda) -> (logits [B,H,W,C] cuda u8|f16, scale, zero_point)`.  The Edge
-TPU tflite model is unavailable here; `SyntheticEngine` produces class scores of the model's exact
-output shape and quantisation.
+`run_logits(input_u8 [B,H,W,3] cuda) -> (logits [B,H,W,C] cuda u8|f16, scale, zero_point)`, or planar
+[B,C,H,W] f32|f16 scores when the engine sets `layout = "nchw"`.  The Edge TPU tflite model is
+unavailable here; `SyntheticEngine` produces class scores of the model's exact output shape and
+quantisation, `TorchvisionEngine` runs a DeepLabv3 network on the GPU.
 """
 import argparse
 import collections
@@ -40,6 +41,42 @@ class SyntheticEngine:
         ch = torch.arange(self.c, device=x.device, dtype=torch.int32)
         q = ((lum.unsqueeze(-1) * (ch * 7 + 3) + ch * 31) % 256).to(torch.uint8)
         return q.contiguous().view(b, self.h, self.w, self.c), self.scale, self.zero_point
+
+
+class TorchvisionEngine:
+    """A logits provider with a real network behind it: torchvision's
+    DeepLabv3-MobileNetV3 with 21 classes, randomly initialised (no checkpoint can be fetched here; pass
+    `state_dict` to load one).  It hands over what the head leaves on the GPU -- planar [B,C,H,W] fp32
+    scores, fp16 with `half=True` -- so the argmax + statistics pass reads it in place
+    (`layout = "nchw"` selects hotpath.argmax_stats_nchw in recognize_and_segment)."""
+
+    layout = "nchw"
+
+    def __init__(self, height=513, width=513, num_classes=21, half=False, device="cuda", seed=0, state_dict=None):
+        import torchvision
+        self.h, self.w, self.c, self.half = height, width, num_classes, half
+        torch.manual_seed(seed)
+        self.model = torchvision.models.segmentation.deeplabv3_mobilenet_v3_large(
+            weights=None, weights_backbone=None, num_classes=num_classes).eval().to(device)
+        if state_dict is not None:
+            self.model.load_state_dict(state_dict)
+        self.mean = torch.tensor([0.485, 0.456, 0.406], device=device).view(1, 3, 1, 1) * 255.0
+        self.std = torch.tensor([0.229, 0.224, 0.225], device=device).view(1, 3, 1, 1) * 255.0
+
+    def get_input_tensor_shape(self):
+        return (1, self.h, self.w, 3)
+
+    @torch.no_grad()
+    def run_logits(self, x):
+        """x: [B,H,W,3] u8 RGB (the output of the pre-process kernel) -> ([B,C,H,W] scores, 1.0, 0)."""
+        inp = (x.permute(0, 3, 1, 2).float() - self.mean) / self.std
+        if self.half:
+            with torch.autocast(device_type=inp.device.type, dtype=torch.float16):
+                out = self.model(inp)["out"]
+            out = out.to(torch.float16)
+        else:
+            out = self.model(inp)["out"]
+        return out.contiguous(), 1.0, 0
 
 
 class ArrayCamera:
@@ -111,7 +148,10 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
             batch = torch.from_numpy(np.stack(frames)).to(dev, non_blocking=True)
             inputs = hotpath.preprocess_frames(batch, geom)                       # :150-161
             logits, scale, zero_point = engine.run_logits(inputs)                 # :162 (model, upstream)
-            label_maps, stats = hotpath.argmax_stats(logits, geom.roi_h, geom.roi_w)   # :163-170, :102-122
+            if getattr(engine, "layout", "nhwc") == "nchw":                       # :163-170, :102-122
+                label_maps, stats = hotpath.argmax_stats_nchw(logits, geom.roi_h, geom.roi_w)
+            else:
+                label_maps, stats = hotpath.argmax_stats(logits, geom.roi_h, geom.roi_w)
             if mode == "contours":
                 masks = hotpath.foreground_mask(label_maps, geom.roi_h, geom.roi_w)   # :173, :79-85
                 masks_h = masks[:, :geom.roi_h, :geom.roi_w].cpu().numpy()
@@ -203,6 +243,8 @@ def build_arg_parser():
     parser.add_argument("--min_area_ratio", type=float, help="segment centroid min area ratio.", default=0.05)
     parser.add_argument("--batch_frames", type=int, default=16, help="frames per GPU pass (new)")
     parser.add_argument("--mode", choices=["contours", "labels"], default="contours", help="object definition (new)")
+    parser.add_argument("--engine", choices=["synthetic", "torchvision", "torchvision-fp16"], default="synthetic",
+                        help="class-score provider standing in for the Edge TPU model (new)")
     parser.add_argument("--port", default="[::]:50051")
     parser.set_defaults(keep_aspect_ratio=True)      # as the reference: always true (:246-259)
     return parser
@@ -213,7 +255,7 @@ def serve(argv=None):
     import grpc
     args = build_arg_parser().parse_args(argv)
     print("Loading {} with {} labels.".format(args.model, args.labels))
-    engine = SyntheticEngine()
+    engine = SyntheticEngine() if args.engine == "synthetic" else TorchvisionEngine(half=args.engine.endswith("fp16"))
     labels = hotpath.load_labels(args.labels)
     cap = cv2.VideoCapture(args.camera_idx)
     camera_res = int(cap.get(cv2.CAP_PROP_FRAME_WIDTH)), int(cap.get(cv2.CAP_PROP_FRAME_HEIGHT))

@@ -43,6 +43,12 @@ def test_argument_validation_before_cuda(ssb):
     assert lib.ssb_argmax_stats_u8(None, 1, 4, 4, 21, 4, 4, None, one, None) == ssb._cabi.SSB_ERR_BAD_POINTER
     assert lib.ssb_argmax_stats_f16(one, 1, 65536, 65536, 19, 4, 4, None, one, None) == ssb._cabi.SSB_ERR_LIMIT
     assert lib.ssb_argmax_stats_u8(one, 0, 4, 4, 21, 4, 4, None, one, None) == 0          # empty batch
+    for fn in (lib.ssb_argmax_stats_nchw_f32, lib.ssb_argmax_stats_nchw_f16):
+        assert fn(one, 1, 4, 4, 21, 4, 5, None, one, None) == ssb._cabi.SSB_ERR_BAD_SHAPE
+        assert fn(one, 1, 4, 4, 300, 4, 4, None, one, None) == ssb._cabi.SSB_ERR_LIMIT
+        assert fn(None, 1, 4, 4, 21, 4, 4, None, one, None) == ssb._cabi.SSB_ERR_BAD_POINTER
+        assert fn(ctypes.c_void_p(17), 1, 4, 4, 21, 4, 4, None, one, None) == ssb._cabi.SSB_ERR_BAD_POINTER   # element alignment
+        assert fn(one, 0, 4, 4, 21, 4, 4, None, one, None) == 0
     assert lib.ssb_preprocess_nearest_u8(one, 1, 4, 4, 48, one, one, 5, 4, one, 4, 4, None) == \
         ssb._cabi.SSB_ERR_BAD_SHAPE
     assert lib.ssb_preprocess_nearest_u8(one, 1, 4, 4, 47, one, one, 4, 4, one, 4, 4, None) == \

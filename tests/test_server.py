@@ -156,3 +156,53 @@ def test_recognize_and_segment_labels_mode(srv, golden):
     for o, w in zip(got, want):
         for a, b in ((o.area, w["area"]), (o.centroid.cx, w["cx"]), (o.centroid.cy, w["cy"]), (o.score, w["score"])):
             assert abs(a - b) <= 1e-6 * max(abs(b), 1e-30)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("half", [False, True])
+def test_recognize_and_segment_with_a_network_as_logits_provider(srv, golden, half):
+    """Row f4: a DeepLabv3 network on the GPU hands planar [B,21,H,W] scores to the planar argmax +
+    statistics kernel; replies are checked against the oracle run on the very scores the network produced."""
+    import torch
+    from oracle import segpath as sp
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    pytest.importorskip("torchvision")
+    lab = golden("labels_colormap.npz")
+    names = dict(zip(lab["label_ids"].tolist(), lab["label_names"].tolist()))
+
+    class Recording(srv.TorchvisionEngine):
+        def run_logits(self, x):
+            out = super().run_logits(x)
+            self.seen.append(out[0].cpu().numpy())
+            return out
+
+    engine = Recording(half=half)
+    engine.seen = []
+    frames = [np.random.default_rng(10 + i).integers(0, 256, (480, 640, 3), dtype=np.uint8) for i in range(3)]
+    srv.recognize_and_segment(True, srv.ArrayCamera(frames), engine, names, 0.0, batch_frames=2, mode="labels")
+    got = list(srv.segmented_objects)
+    srv.segmented_objects.clear()
+    assert [s.shape for s in engine.seen] == [(2, 21, 513, 513), (1, 21, 513, 513)]
+    assert engine.seen[0].dtype == (np.float16 if half else np.float32)
+    want, n_px = [], 0
+    for scores in engine.seen:
+        _, st = sp.argmax_stats_nchw(scores, 384, 513)                      # 640x480 -> 513x384 inside 513x513
+        n_px += int(st[:, :, 0].sum())
+        for i in range(scores.shape[0]):
+            want = sp.per_label_objects(st[i], 513, 513, names, 0.0, 1.0, 0, fixed_shift=24) + want
+    assert n_px == 3 * 384 * 513
+    assert [o.label for o in got] == [w["label"] for w in want]
+    for o, w in zip(got, want):
+        for a, b in ((o.area, w["area"]), (o.centroid.cx, w["cx"]), (o.centroid.cy, w["cy"]), (o.score, w["score"])):
+            assert abs(a - b) <= 1e-6 * max(abs(b), 1e-30)
+
+
+def test_network_logits_provider_shapes_on_cpu(srv):
+    """The provider itself needs no GPU: planar scores of the model-input size."""
+    import torch
+    pytest.importorskip("torchvision")
+    e = srv.TorchvisionEngine(height=65, width=65, device="cpu")
+    out, scale, zp = e.run_logits(torch.zeros((2, 65, 65, 3), dtype=torch.uint8))
+    assert out.shape == (2, 21, 65, 65) and out.dtype == torch.float32 and out.is_contiguous()
+    assert (scale, zp) == (1.0, 0) and e.layout == "nchw" and e.get_input_tensor_shape() == (1, 65, 65, 3)
