@@ -385,7 +385,7 @@ def run_ssb(args):
                        "host_numa_binding_cores_rank0": numa_cores},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "argmax_stats_stream_kernel<CodecU8<21>,8,3>",
+                         "kernel": "argmax_stats_stream_kernel<CodecU8<21>,4,2>",
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": threads, "kind": "port",
