@@ -207,6 +207,26 @@ def other_kernels(ssb200, torch):
     out.append({"kernel": "argmax_stats u8, blobby label maps (batch 64, one batch re-read: L2 holds 1/3 of it)", "us": us,
                 "frames_per_s": b / us * 1e6, "GBps": ALGO_BYTES_PER_FRAME * b / us / 1e3})
     del qb, field, lab_true
+    # config 3 as one unit: 256 camera frames -> K1 -> model input, and the post-process of 256 frames with
+    # the 16:9 crop (the class scores are synthetic: the model between the two is not part of the path)
+    b = 256
+    cam = torch.randint(0, 256, (b, 1080, 1920, 3), dtype=torch.uint8, device="cuda", generator=g)
+    rgb3 = torch.empty((b, H, W, 3), dtype=torch.uint8, device="cuda")
+    q3 = torch.randint(0, 256, (b, H, W, C), dtype=torch.uint8, device="cuda", generator=g)
+    lab3 = torch.empty((b, H, W), dtype=torch.uint8, device="cuda")
+    st3 = torch.empty((b, C, 4), dtype=torch.int64, device="cuda")
+
+    def cfg3(i):
+        ssb200.preprocess_frames(cam, geom, out=rgb3)
+        ssb200.argmax_stats(q3, CAM_ROI_H, CAM_ROI_W, labels=lab3, stats=st3)
+    us = _time_us(torch, cfg3, 20)
+    us_k1 = _time_us(torch, lambda i: ssb200.preprocess_frames(cam, geom, out=rgb3), 20)
+    sector3 = (geom.new_h * 1920 * 3 + H * W * 3) * b
+    out.append({"kernel": "config3: 256 x 1080p frames, preprocess + argmax_stats (ROI 288x513)", "us": us,
+                "frames_per_s": b / us * 1e6, "us_preprocess_alone": us_k1,
+                "preprocess_frac_of_measured_peak": sector3 / us_k1 / 1e3 / peak,
+                "GBps_sector_effective_both": (sector3 + ALGO_BYTES_PER_FRAME * b) / us / 1e3})
+    del cam, rgb3, q3
     # planar scores left on the GPU by a convolutional head (row f4): fp32 and fp16 [B,21,513,513]
     for dt, nb in ((torch.float32, 32), (torch.float16, 64)):
         pl = [torch.randn((nb, C, H, W), dtype=dt, device="cuda", generator=g) for _ in range(2)]

@@ -15,13 +15,21 @@ WANT = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'sm__inst_executed_pipe_tensor.sum']
 
 
+def short_name(k):
+    """`void ssb::<unnamed>::kernel<...>(Params)` -> `kernel<...>` without namespaces."""
+    import re
+    k = re.sub(r'unnamed>::|ssb::|^void ', '', k)   # ncu prints `<unnamed>::` without its opening bracket
+    return k.split('(')[0][:70]
+
+
 def main(rep, out, title):
     raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
     ki = hdr.index('Kernel Name')
     lines = ['# ' + title, '# kernels: ' + ' | '.join(sorted({r[ki][:100] for r in data})),
-             'metric,unit,' + ','.join('launch_%d' % i for i in range(len(data)))]
+             'metric,unit,' + ','.join('launch_%d' % i for i in range(len(data))),
+             'kernel,,' + ','.join('"%s"' % short_name(r[ki]) for r in data)]
     for w in WANT:
         if w in hdr:
             i = hdr.index(w)
