@@ -18,7 +18,7 @@ WANT = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
 def short_name(k):
     """`void ssb::<unnamed>::kernel<...>(Params)` -> `kernel<...>` without namespaces."""
     import re
-    k = re.sub(r'unnamed>::|ssb::|^void ', '', k)   # ncu prints `<unnamed>::` without its opening bracket
+    k = re.sub(r'<unnamed>::|unnamed>::|ssb::|^void ', '', k)   # some ncu pages print `<unnamed>::` without its opening bracket
     return k.split('(')[0][:70]
 
 
@@ -27,6 +27,7 @@ def main(rep, out, title):
     rows = list(csv.reader(raw.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
     ki = hdr.index('Kernel Name')
+    data = [r for r in data if 'at::' not in r[ki]]   # torch's own kernels (input generation) are not ours
     lines = ['# ' + title, '# kernels: ' + ' | '.join(sorted({r[ki][:100] for r in data})),
              'metric,unit,' + ','.join('launch_%d' % i for i in range(len(data))),
              'kernel,,' + ','.join('"%s"' % short_name(r[ki]) for r in data)]
