@@ -13,11 +13,12 @@
 //     tile (C copies of ~1 KB at arbitrary 16-byte phase, aligned supersets, a plain-load tail for the
 //     last bytes of the tensor) was built first and measured slower at every ring shape, bound by
 //     issuing C small copies per tile (profiles/experiments/r01_nchw_ring_vs_direct.log);
-//   * a tile is 128*NWARPS consecutive pixels of ONE frame (the last tile of a frame is partial); a
-//     thread issues all its loads of a tile before the first comparison.
+//   * a tile is NWARPS chunks of 128 (fp32) or 256 (fp16) consecutive pixels of ONE frame, one chunk per
+//     warp (the last tile of a frame is partial); a thread issues all its loads of a tile before the
+//     first comparison.
 // fp32: lane l of warp w owns pixels 128*w + 32*j + l (j = 0..3), one 4-byte load per score.
 // fp16: one 2-byte load per score is bound by load instructions in flight, not bytes (3.9 TB/s), so a
-//   lane owns the pixel PAIRS 128*w + 64*jj + 2*l + {0,1} (jj = 0,1) and loads a pair as one aligned
+//   lane owns the pixel PAIRS 256*w + 64*jj + 2*l + {0,1} (jj = 0..3) and loads a pair as one aligned
 //   32-bit word, compared as half2.  A plane whose first element sits at an odd element index has its
 //   aligned words one pixel to the left of the pairs; such planes keep their own running maximum over
 //   the shifted pairs (2*l-1, 2*l) and the two are merged once per tile with three shuffles (plus a
@@ -49,12 +50,14 @@ struct PlanarParams {
 };
 
 // Packed lane-private word of this file:  n[0,8)  Σb[8,16)  Σk[24,38)  Σa[38,48)  Σdy[48,64)
-// where a pixel's offset inside its warp's 128-pixel chunk is  kA*a + b + kLane*lane.
+// where a pixel's offset inside its warp's chunk is  kA*a + b + kLane*lane.
 constexpr int kFieldB = 8;
 
 struct PlaneF32 {
     using Elem = ElemF32;
     static constexpr int kBytes = 4;
+    static constexpr int kPx = 4;                                  // pixels per lane and tile
+    static constexpr int kDefaultWarps = 8;                        // best of the compiled set on B200 (tools/bench_nchw.py)
     static constexpr int kA = 32, kLane = 1;                       // offset = 32*j + lane
     static __device__ __forceinline__ int field_a(int j) { return j; }
     static __device__ __forceinline__ int field_b(int) { return 0; }
@@ -66,6 +69,8 @@ struct PlaneF32 {
 struct PlaneF16 {
     using Elem = ElemF16;
     static constexpr int kBytes = 2;
+    static constexpr int kPx = 8;                                  // 4 pair words per plane in flight: as many bytes per thread as fp32
+    static constexpr int kDefaultWarps = 4;
     static constexpr int kA = 64, kLane = 2;                       // offset = 64*(j>>1) + 2*lane + (j&1)
     static __device__ __forceinline__ int field_a(int j) { return j >> 1; }
     static __device__ __forceinline__ int field_b(int j) { return j & 1; }
@@ -144,18 +149,18 @@ __device__ __forceinline__ const char *next_plane(const char *pc, long long plan
     return reinterpret_cast<const char *>(a);
 }
 
-// One load per score.  `lgw` points at plane 0 of the warp's 128-pixel chunk; pixels at or beyond
+// One load per score.  `lgw` points at plane 0 of the warp's chunk; pixels at or beyond
 // `n_chunk` (pixels of the chunk inside the frame) are not loaded.
 template <typename P, int C, bool FULL>
 __device__ __forceinline__ void classify_scalar(const typename P::Elem::T *lgw, long long hw, int lane, int n_chunk,
-                                                uint32_t (&best)[4], uint32_t (&lab)[4]) {
+                                                uint32_t (&best)[P::kPx], uint32_t (&lab)[P::kPx]) {
     // one running BYTE pointer per thread (a 64-bit add per plane); everything else is an immediate
     const char *pc = reinterpret_cast<const char *>(lgw + P::kLane * lane);
     const long long plane_bytes = hw * P::kBytes;
 #pragma unroll
     for (int c = 0; c < C; ++c, pc = next_plane(pc, plane_bytes)) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < P::kPx; ++j) {
             const int off = pixel_offset<P>(j, lane);
             uint32_t v = 0u;
             if (FULL || off < n_chunk)
@@ -181,9 +186,10 @@ __device__ __forceinline__ uint32_t hgt2_mask_bits(uint32_t a, uint32_t b) {
 // odd channel index do.  The other planes ("shifted") are read through the aligned words that hold
 // pixels (2l-1, 2l) and merged at the end.
 template <int C, int MODE>
-__device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw, int lane, uint32_t (&best)[4],
-                                               uint32_t (&lab)[4]) {
-    uint32_t bA[2], lA[2], bB[2], lB[2], bX = 0u, lX = 0u;
+__device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw, int lane, uint32_t (&best)[PlaneF16::kPx],
+                                               uint32_t (&lab)[PlaneF16::kPx]) {
+    constexpr int NJ = PlaneF16::kPx / 2, kChunk = 32 * PlaneF16::kPx;   // pair words per plane, pixels per warp
+    uint32_t bA[NJ], lA[NJ], bB[NJ], lB[NJ], bX = 0u, lX = 0u;
     bool haveA = false, haveB = false;
     const char *pc = reinterpret_cast<const char *>(lgw + 2 * lane);   // running byte pointer, see classify_scalar
     const long long plane_bytes = hw * 2;
@@ -194,7 +200,7 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
         const uint32_t cc = static_cast<uint32_t>(c) * 0x00010001u;
         if (aligned) {
 #pragma unroll
-            for (int jj = 0; jj < 2; ++jj) {
+            for (int jj = 0; jj < NJ; ++jj) {
                 const uint32_t v = __ldg(reinterpret_cast<const unsigned int *>(q + 64 * jj));
                 if (!haveA) {
                     bA[jj] = v;
@@ -208,7 +214,7 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
             haveA = true;
         } else {
 #pragma unroll
-            for (int jj = 0; jj < 2; ++jj) {
+            for (int jj = 0; jj < NJ; ++jj) {
                 const uint32_t v = __ldg(reinterpret_cast<const unsigned int *>(q + 64 * jj - 1));
                 if (!haveB) {
                     bB[jj] = v;
@@ -219,9 +225,9 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
                     lB[jj] = (cc & m) | (lB[jj] & ~m);
                 }
             }
-            // pixel 127 of the chunk is in none of the shifted words: lane 31 tracks it on its own
+            // the last pixel of the chunk is in none of the shifted words: lane 31 tracks it on its own
             uint32_t x = 0u;
-            if (lane == 31) x = __ldg(q + 65);   // pixel 127: q already holds 2*31
+            if (lane == 31) x = __ldg(q + (kChunk - 1 - 62));   // q already holds 2*31
             if (!haveB) {
                 bX = x;
                 lX = static_cast<uint32_t>(c);
@@ -235,28 +241,28 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
     }
     if constexpr (MODE == 0) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 2 * NJ; ++j) {
             best[j] = (bA[j >> 1] >> (16 * (j & 1))) & 0xFFFFu;
             lab[j] = (lA[j >> 1] >> (16 * (j & 1))) & 0xFFFFu;
         }
     } else {
     // shifted word of lane l holds pixels (2l-1, 2l): pixel 2l is its high half, pixel 2l+1 the low
     // half of lane l+1's word (lane 31: lane 0's word of the next 64-pixel half, or the scalar)
-    uint32_t nB[2], nL[2];
+    uint32_t nB[NJ], nL[NJ];
 #pragma unroll
-    for (int jj = 0; jj < 2; ++jj) {
+    for (int jj = 0; jj < NJ; ++jj) {
         nB[jj] = __shfl_down_sync(0xffffffffu, bB[jj], 1);
         nL[jj] = __shfl_down_sync(0xffffffffu, lB[jj], 1);
-    }
-    const uint32_t wb = __shfl_sync(0xffffffffu, bB[1], 0), wl = __shfl_sync(0xffffffffu, lB[1], 0);
-    if (lane == 31) {
-        nB[0] = wb;
-        nL[0] = wl;
-        nB[1] = bX;
-        nL[1] = lX;
+        // lane 31's right neighbour: lane 0's word of the next 64-pixel run, or the scalar at the chunk's end
+        const uint32_t wb = jj + 1 < NJ ? __shfl_sync(0xffffffffu, bB[jj + 1 < NJ ? jj + 1 : jj], 0) : bX;
+        const uint32_t wl = jj + 1 < NJ ? __shfl_sync(0xffffffffu, lB[jj + 1 < NJ ? jj + 1 : jj], 0) : lX;
+        if (lane == 31) {
+            nB[jj] = wb;
+            nL[jj] = wl;
+        }
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < 2 * NJ; ++j) {
         const int jj = j >> 1, h = j & 1;
         const uint32_t vA = (bA[jj] >> (16 * h)) & 0xFFFFu, cA = (lA[jj] >> (16 * h)) & 0xFFFFu;
         const uint32_t vB = h ? (nB[jj] & 0xFFFFu) : (bB[jj] >> 16), cB = h ? (nL[jj] & 0xFFFFu) : (lB[jj] >> 16);
@@ -272,7 +278,7 @@ __device__ __forceinline__ void classify_pairs(const uint16_t *lgw, long long hw
 template <typename P, int C, int NWARPS, int MINB>
 __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(const PlanarParams p) {
     using T = typename P::Elem::T;
-    constexpr int kThreads = NWARPS * 32, kTilePx = NWARPS * 128;
+    constexpr int kThreads = NWARPS * 32, kPx = P::kPx, kChunk = 32 * kPx, kTilePx = NWARPS * kChunk;
     constexpr int kHistWarpBytes = C * 32 * 16, kHistBytes = NWARPS * kHistWarpBytes;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t *hist_all = smem;
@@ -297,7 +303,7 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
     uint8_t *hist = hist_all + warp * kHistWarpBytes;
     unsigned long long *blk_w = blk + warp * C * 4;
     const uint32_t hist_lane = smem_addr(hist) + lane * 16;
-    // the lane-private histograms hold pixels of frame f_acc at r_base + k*TILE + 128*warp + offset(a, b, lane),
+    // the lane-private histograms hold pixels of frame f_acc at r_base + k*TILE + CHUNK*warp + offset(a, b, lane),
     // rows >= y_base
     long long f_acc = f;
     int r_base = i * kTilePx;
@@ -310,7 +316,7 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
         for (int l = lane; l < C; l += 32) {
             const PlanarTotals t = planar_row_totals(hist, l, lane);
             if (t.n) {
-                const long long sr = t.n * r_base + t.sk * kTilePx + 128ll * warp * t.n + P::kA * t.sa + t.sb + P::kLane * t.cw;
+                const long long sr = t.n * r_base + t.sk * kTilePx + static_cast<long long>(kChunk) * warp * t.n + P::kA * t.sa + t.sb + P::kLane * t.cw;
                 const long long sy = t.n * y_base + t.sdy;
                 unsigned long long *row = blk_w + l * 4;
                 row[SSB_STAT_N] += static_cast<unsigned long long>(t.n);
@@ -373,9 +379,9 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
             k = 0;
         }
         const int n_valid = min(kTilePx, p.hw - r0);       // pixels of the tile inside the frame
-        const int n_chunk = n_valid - 128 * warp;           // ... of this warp's 128-pixel chunk (may be <= 0)
-        const T *lgw = static_cast<const T *>(p.logits) + (f * C * p.hw + r0 + 128 * warp);
-        uint32_t best[4], lab[4];
+        const int n_chunk = n_valid - kChunk * warp;        // ... of this warp's chunk (may be <= 0)
+        const T *lgw = static_cast<const T *>(p.logits) + (f * C * p.hw + r0 + kChunk * warp);
+        uint32_t best[kPx], lab[kPx];
         if (n_valid == kTilePx) {
             if constexpr (P::kBytes == 2) {
                 if (p.pairs_ok) {
@@ -394,9 +400,9 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
         }
 
         if (p.labels) {
-            uint8_t *out = p.labels + f * p.hw + r0 + 128 * warp;
+            uint8_t *out = p.labels + f * p.hw + r0 + kChunk * warp;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kPx; ++j) {
                 const int off = pixel_offset<P>(j, lane);
                 if (off < n_chunk)
                     asm volatile("st.global.L2::cache_hint.u8 [%0], %1, %2;" ::"l"(out + off), "r"(lab[j]), "l"(pol_keep) : "memory");
@@ -408,29 +414,32 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
         // every pixel.
         if (n_valid == kTilePx && p.roi_w == p.w &&
             fastdiv(static_cast<uint32_t>(r0 + kTilePx - 1), p.divw) < static_cast<uint32_t>(p.roi_h)) {
-            uint32_t add_lo[4], add_hi[4];
+            uint32_t add_lo[kPx], add_hi[kPx];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const uint32_t y = fastdiv(static_cast<uint32_t>(r0 + 128 * warp + pixel_offset<P>(j, lane)), p.divw);
+            for (int j = 0; j < kPx; ++j) {
+                const uint32_t y = fastdiv(static_cast<uint32_t>(r0 + kChunk * warp + pixel_offset<P>(j, lane)), p.divw);
                 add_lo[j] = 1u | (static_cast<uint32_t>(P::field_b(j)) << kFieldB) | (static_cast<uint32_t>(k) << kFieldK);
                 add_hi[j] = (static_cast<uint32_t>(P::field_a(j)) << (kFieldJ - 32)) | ((y - y_base) << (kFieldDy - 32));
             }
-            planar_add2<P>(hist_lane, lab[0], lab[1], best[0], best[1], add_lo[0], add_lo[1], add_hi[0], add_hi[1], true, true);
-            planar_add2<P>(hist_lane, lab[2], lab[3], best[2], best[3], add_lo[2], add_lo[3], add_hi[2], add_hi[3], true, true);
-        } else if (fastdiv(static_cast<uint32_t>(r0), p.divw) < static_cast<uint32_t>(p.roi_h)) {
-            uint32_t add_lo[4], add_hi[4];
-            bool counted[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kPx; j += 2)
+                planar_add2<P>(hist_lane, lab[j], lab[j + 1], best[j], best[j + 1], add_lo[j], add_lo[j + 1], add_hi[j], add_hi[j + 1], true, true);
+        } else if (fastdiv(static_cast<uint32_t>(r0), p.divw) < static_cast<uint32_t>(p.roi_h)) {
+            uint32_t add_lo[kPx], add_hi[kPx];
+            bool counted[kPx];
+#pragma unroll
+            for (int j = 0; j < kPx; ++j) {
                 const int off = pixel_offset<P>(j, lane);
-                const uint32_t r = static_cast<uint32_t>(r0 + 128 * warp + off);
+                const uint32_t r = static_cast<uint32_t>(r0 + kChunk * warp + off);
                 const uint32_t y = fastdiv(r, p.divw), x = r - y * p.w;
                 counted[j] = (off < n_chunk) & (x < static_cast<uint32_t>(p.roi_w)) & (y < static_cast<uint32_t>(p.roi_h));
                 add_lo[j] = 1u | (static_cast<uint32_t>(P::field_b(j)) << kFieldB) | (static_cast<uint32_t>(k) << kFieldK);
                 add_hi[j] = (static_cast<uint32_t>(P::field_a(j)) << (kFieldJ - 32)) | ((y - y_base) << (kFieldDy - 32));
             }
-            planar_add2<P>(hist_lane, lab[0], lab[1], best[0], best[1], add_lo[0], add_lo[1], add_hi[0], add_hi[1], counted[0], counted[1]);
-            planar_add2<P>(hist_lane, lab[2], lab[3], best[2], best[3], add_lo[2], add_lo[3], add_hi[2], add_hi[3], counted[2], counted[3]);
+#pragma unroll
+            for (int j = 0; j < kPx; j += 2)
+                planar_add2<P>(hist_lane, lab[j], lab[j + 1], best[j], best[j + 1], add_lo[j], add_lo[j + 1], add_hi[j], add_hi[j + 1], counted[j],
+                               counted[j + 1]);
         }
         covered += n_valid;
         ++k;
@@ -444,7 +453,7 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
 template <typename P, int C, int NWARPS, int MINB>
 int launch_planar(PlanarParams p, cudaStream_t st) {
     auto kern = argmax_stats_planar_kernel<P, C, NWARPS, MINB>;
-    constexpr int kTilePx = NWARPS * 128;
+    constexpr int kTilePx = NWARPS * 32 * P::kPx;
     constexpr int kSmem = NWARPS * C * 32 * 16 + NWARPS * C * 4 * 8;
     DeviceInfo di;
     if (int rc = device_info(&di)) return rc;
@@ -462,7 +471,7 @@ int launch_planar(PlanarParams p, cudaStream_t st) {
     }
     p.tiles_per_frame = (p.hw + kTilePx - 1) / kTilePx;
     p.n_tiles = static_cast<long long>(p.B) * p.tiles_per_frame;
-    p.flush_tiles = pick_flush_tiles(kTilePx, p.w);
+    p.flush_tiles = min(pick_flush_tiles(kTilePx, p.w), 252 / P::kPx);   // the 8-bit n field: <= 252 pixels per lane and period
     if (p.flush_tiles < 1) return fail(SSB_ERR_LIMIT, "W=%d too narrow for the packed accumulators", p.w);
     long long grid = static_cast<long long>(di.sm_count) * ctas_per_sm[dev];
     if (const char *env = getenv("SSB_ARGMAX_WAVES")) grid *= atoi(env) > 0 ? atoi(env) : 1;  // tuning knob
@@ -487,7 +496,7 @@ int argmax_stats_planar(const void *logits, int B, int H, int W, int C, int roi_
     if (B == 0) return SSB_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     auto *stats64 = reinterpret_cast<unsigned long long *>(stats);
-    int nw = 8;   // best of the compiled set on B200 (tools/bench_nchw.py)
+    int nw = P::kDefaultWarps;
     bool force_generic = false;
     if (const char *env = getenv("SSB_ARGMAX_NCHW_CFG")) {   // tuning knob (benchmarks only): warps per CTA, or "generic"
         if (!strcmp(env, "generic")) force_generic = true;
@@ -495,7 +504,7 @@ int argmax_stats_planar(const void *logits, int B, int H, int W, int C, int roi_
     }
     // the unrolled kernel exists for the class counts of the two model families; everything else
     // (and frames too narrow for the packed counters) takes the generic kernel
-    const bool fast = !force_generic && (C == 19 || C == 21) && W >= 2;
+    const bool fast = !force_generic && (C == 19 || C == 21) && W >= 2 && pick_flush_tiles(nw * 32 * P::kPx, W) >= 1;
     if (!fast) {
         SSB_CUDA_TRY(cudaMemsetAsync(stats64, 0, sizeof(uint64_t) * 4 * C * static_cast<size_t>(B), st));
         return launch_generic<E>(static_cast<const typename E::T *>(logits), B, H, W, C, roi_h, roi_w, labels, stats64, st,
