@@ -255,8 +255,19 @@ def other_kernels(ssb200, torch):
         one(i)
         torch.cuda.synchronize()
     wall_us = (time.perf_counter() - t0) / 200 * 1e6
+    # the same two launches recorded once into a CUDA graph and replayed
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        one(0)
+    us_g = _time_us(torch, lambda i: graph.replay(), 200)
+    t0 = time.perf_counter()
+    for i in range(200):
+        graph.replay()
+        torch.cuda.synchronize()
+    wall_g = (time.perf_counter() - t0) / 200 * 1e6
     out.append({"kernel": "config1: single 513x513 frame, preprocess + argmax_stats", "us_device_back_to_back": us,
-                "us_host_launch_to_sync": wall_us})
+                "us_host_launch_to_sync": wall_us, "us_device_back_to_back_graph_replay": us_g,
+                "us_host_launch_to_sync_graph_replay": wall_g})
     return out
 
 

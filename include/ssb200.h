@@ -11,8 +11,12 @@
  *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
  *   - the caller owns every input/output buffer and `stats` needs no initialisation.  The only device
  *     memory the library owns is a small zero-at-rest scratch pool per device (a few hundred KB,
- *     cudaMalloc'ed on first use or when a larger batch than ever before arrives -- warm it up
- *     outside stream capture) and the ssb_pipeline objects the caller creates explicitly;
+ *     cudaMalloc'ed on first use or when a larger batch than ever before arrives) and the
+ *     ssb_pipeline objects the caller creates explicitly;
+ *   - CUDA graphs: every device-pointer entry point except ssb_argmax_stats_u8_noalloc may be called
+ *     while `stream` is being captured, after the same call (same or larger batch) has run once
+ *     outside capture.  A recorded argmax call keeps a scratch block of its own for the life of the
+ *     process (at most 16 recorded calls per device; SSB_ERR_LIMIT otherwise);
  *   - all work is enqueued on `stream` (a cudaStream_t passed as void*, 0 = legacy default stream)
  *     of the CURRENT device; calls are asynchronous with respect to the host and never
  *     synchronise the device; re-entrant across (device, stream) pairs;

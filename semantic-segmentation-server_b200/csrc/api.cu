@@ -28,7 +28,7 @@ int device_info(DeviceInfo *out) {
 }
 
 namespace {
-constexpr int kMaxDevices = 64, kSlots = 8;
+constexpr int kMaxDevices = 64, kSlots = 8, kCaptureSlots = 16;
 struct Slot {
     void *ptr = nullptr;
     size_t bytes = 0;
@@ -36,12 +36,29 @@ struct Slot {
     cudaStream_t last_stream = nullptr;
     bool used = false;
 };
+// Scratch for calls recorded into a CUDA graph.  Such a call bakes its scratch pointer into the graph and
+// may be replayed at any later time, so it gets a block of its own for good (never shared with eager
+// calls or with another recorded call).  Nothing can be allocated while a stream is being captured:
+// the blocks that are still free are (re)sized by EAGER calls, to the largest request seen so far.
+struct CaptureSlot {
+    void *ptr = nullptr;
+    size_t bytes = 0;
+    bool owned = false;
+};
 struct Pool {
     std::mutex mu;
     Slot slots[kSlots];
     unsigned next = 0;
+    CaptureSlot capture[kCaptureSlots];
+    size_t capture_bytes = 0;
 };
 Pool g_pools[kMaxDevices];
+
+int alloc_zeroed(void **ptr, size_t bytes) {
+    SSB_CUDA_TRY(cudaMalloc(ptr, bytes));
+    SSB_CUDA_TRY(cudaMemset(*ptr, 0, bytes));
+    return SSB_OK;
+}
 }  // namespace
 
 int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out) {
@@ -50,6 +67,36 @@ int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out) {
     if (dev < 0 || dev >= kMaxDevices) return fail(SSB_ERR_LIMIT, "device ordinal %d not supported", dev);
     Pool &pool = g_pools[dev];
     std::lock_guard<std::mutex> lock(pool.mu);
+    cudaStreamCaptureStatus capturing = cudaStreamCaptureStatusNone;
+    SSB_CUDA_TRY(cudaStreamIsCapturing(stream, &capturing));
+    if (capturing != cudaStreamCaptureStatusNone) {
+        for (int i = 0; i < kCaptureSlots; ++i) {
+            CaptureSlot &c = pool.capture[i];
+            if (!c.owned && c.bytes >= bytes) {
+                c.owned = true;   // for the life of the process: the graph may be replayed at any time
+                out->ptr = c.ptr;
+                out->dev = dev;
+                out->slot = -1;
+                return SSB_OK;
+            }
+        }
+        return fail(SSB_ERR_LIMIT,
+                    "no scratch block of %zu bytes for a call recorded into a CUDA graph: run the same call once outside "
+                    "stream capture first (at most %d recorded calls per device)", bytes, kCaptureSlots);
+    }
+    const size_t want = (bytes + 65535) / 65536 * 65536;
+    if (pool.capture_bytes < want) {   // keep the free capture blocks as large as the largest eager request
+        for (int i = 0; i < kCaptureSlots; ++i) {
+            CaptureSlot &c = pool.capture[i];
+            if (c.owned) continue;
+            if (c.ptr) SSB_CUDA_TRY(cudaFree(c.ptr));
+            c.ptr = nullptr;
+            c.bytes = 0;
+            if (int rc = alloc_zeroed(&c.ptr, want)) return rc;
+            c.bytes = want;
+        }
+        pool.capture_bytes = want;
+    }
     const int idx = static_cast<int>(pool.next++ % kSlots);
     Slot &s = pool.slots[idx];
     if (!s.done) SSB_CUDA_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
@@ -58,9 +105,7 @@ int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out) {
         if (s.ptr) SSB_CUDA_TRY(cudaFree(s.ptr));
         s.ptr = nullptr;
         s.bytes = 0;
-        const size_t want = (bytes + 65535) / 65536 * 65536;
-        SSB_CUDA_TRY(cudaMalloc(&s.ptr, want));
-        SSB_CUDA_TRY(cudaMemset(s.ptr, 0, want));
+        if (int rc = alloc_zeroed(&s.ptr, want)) return rc;
         s.bytes = want;
         s.used = false;
     }
@@ -72,6 +117,7 @@ int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out) {
 }
 
 int workspace_release(const WorkspaceLease &lease, cudaStream_t stream) {
+    if (lease.slot < 0) return SSB_OK;   // block owned by a recorded call: ordered by the graph itself
     Pool &pool = g_pools[lease.dev];
     std::lock_guard<std::mutex> lock(pool.mu);
     Slot &s = pool.slots[lease.slot];

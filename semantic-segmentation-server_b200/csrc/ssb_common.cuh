@@ -41,9 +41,11 @@ int device_info(DeviceInfo *out);
 
 // ---- scratch workspaces ------------------------------------------------------------------------
 // Device scratch that is ZERO AT REST (kernels leave it zeroed).  A small per-device pool, grown on
-// demand with cudaMalloc (first use, or a larger request than seen before: do that outside stream
-// capture).  A slot that was last used on another stream is ordered behind that use with an event,
-// so concurrent streams never share live scratch.
+// demand with cudaMalloc (first use, or a larger request than seen before).  A slot that was last
+// used on another stream is ordered behind that use with an event, so concurrent streams never share
+// live scratch.  A call made while its stream is being captured into a CUDA graph gets a block of its
+// own that no other call ever uses (slot == -1 in the lease); those blocks are sized by earlier eager
+// calls, so the same call must have run once outside capture.
 struct WorkspaceLease {
     void *ptr;
     int dev, slot;
