@@ -370,6 +370,8 @@ def run_ssb(args):
         pipe.argmax_stats(pinned[i % 2].numpy(), ROI_H, ROI_W, labels_out=out_labels, stats_out=out_stats)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    if os.environ.get("BENCH_DEBUG"):
+        sys.stderr.write("rank %d e2e %.1f ms for %d steps\n" % (rank, e2e_s * 1e3, e2e_steps))
     barrier()
     want_l, want_s = cport.argmax_stats(host_batches[(e2e_steps - 1) % 2][-1:], ROI_H, ROI_W)
     if not ((out_labels[-1:] == want_l).all() and (out_stats[-1:] == want_s).all()):
