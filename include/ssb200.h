@@ -157,6 +157,30 @@ SSB_API int ssb_argmax_stats_u8_noalloc(const uint8_t *logits, int B, int H, int
 SSB_API int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int roi_h, int roi_w,
                    const uint8_t *colormap, uint8_t *mask, void *stream);
 
+/* Replaces the per-contour fill of sem_seg_server.py:98-111 (filled contour mask -> label pixels under
+ * it -> bincount -> majority label and its share) with one table per frame: the connected regions of
+ * the mask inside the ROI -- 8-connected foreground, 4-connected background, as cv2.findContours sees
+ * them -- each with its first pixel in raster order, the region that encloses it, and the histogram
+ * of the label map over its own pixels.  The pixels OpenCV fills for the outer contour of a
+ * foreground region are that region plus everything enclosed by it, so the host sums the table along
+ * the enclosure tree (Python: ssb200.objects_from_regions); polygon area and moments (:93, :115)
+ * stay with OpenCV.
+ *
+ *   mask, labels [B][H][W] u8 (ssb_fg_mask_u8 / ssb_argmax_stats_* outputs); label values >= C are not counted
+ *   scratch      ssb_blob_regions_scratch_bytes(B, roi_h, roi_w) bytes of device memory, contents ignored
+ *   count        [B] regions found; a frame with count > max_regions has an incomplete table (use the
+ *                per-contour fill for that frame)
+ *   first        [B][max_regions] first pixel of the region, y*roi_w + x (row order is arbitrary)
+ *   parent       [B][max_regions] first pixel of the enclosing region = the region of the pixel left
+ *                of `first`; -1 when `first` is in column 0
+ *   flags        [B][max_regions] bit 0: foreground region; bit 1: background region touching the ROI
+ *                border (not a hole: it is the outside)
+ *   hist         [B][max_regions][C] u32 label histogram of the region's own pixels */
+SSB_API size_t ssb_blob_regions_scratch_bytes(int B, int roi_h, int roi_w);
+SSB_API int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, int B, int H, int W, int roi_h, int roi_w,
+                        int C, int max_regions, void *scratch, int32_t *count, int32_t *first, int32_t *parent,
+                        int32_t *flags, uint32_t *hist, void *stream);
+
 /* Host-buffer convenience for callers that hold frames/logits in host memory (the reference's
  * situation: cap.read() and engine.run_inference both return host arrays).
  *

@@ -246,6 +246,90 @@ def objects_from_contours(mask, segment_img, min_area, labels):
     return objs
 
 
+def blob_regions(masks, label_maps, roi_h, roi_w, num_classes=21, max_regions=256, stream=None):
+    """[B,H,W] u8 masks + label maps (device) -> region tables of every frame's ROI, as a dict of device
+    tensors: count [B], first / parent / flags [B,R] int32, hist [B,R,num_classes] int32 (C-ABI:
+    ssb_blob_regions_u8).  Copy them to the host and hand one frame's rows to objects_from_regions."""
+    _require_cuda(masks, "masks")
+    _require_cuda(label_maps, "label_maps")
+    b, h, w = masks.shape
+    dev = masks.device
+    scratch = torch.empty(_cabi.lib.ssb_blob_regions_scratch_bytes(b, roi_h, roi_w), dtype=torch.uint8, device=dev)
+    t = {"count": torch.empty((b,), dtype=torch.int32, device=dev),
+         "first": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
+         "parent": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
+         "flags": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
+         "hist": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev)}
+    with torch.cuda.device(dev):
+        _cabi.check(_cabi.lib.ssb_blob_regions_u8(
+            masks.data_ptr(), label_maps.data_ptr(), b, h, w, roi_h, roi_w, num_classes, max_regions, scratch.data_ptr(),
+            t["count"].data_ptr(), t["first"].data_ptr(), t["parent"].data_ptr(), t["flags"].data_ptr(),
+            t["hist"].data_ptr(), _stream_ptr(stream)))
+    return t
+
+
+def fold_region_histograms(count, first, parent, flags, hist):
+    """One frame's region table (host numpy) -> {first pixel of a foreground region: label histogram of
+    everything its outer contour encloses} -- the region itself, its holes, and whatever is nested in
+    them; None if the table is incomplete (count > rows).  A region's children all have larger first
+    pixels than it, so one pass in descending order of first pixel folds every subtree."""
+    n = int(count)
+    if n > first.shape[0]:
+        return None
+    first, parent, flags = first[:n], parent[:n], flags[:n]
+    enc = hist[:n].astype(np.int64)
+    row_of = {int(p): i for i, p in enumerate(first)}
+    for i in np.argsort(-first):
+        is_fg, outside = flags[i] & 1, (flags[i] & 2) and not (flags[i] & 1)
+        if outside or parent[i] < 0:
+            continue                                   # the outside, or a region in column 0: nothing encloses it
+        j = row_of[int(parent[i])]
+        if (flags[j] & 2) and not (flags[j] & 1):
+            continue                                   # enclosed by the outside only
+        enc[j] += enc[i]
+    return {int(first[i]): enc[i] for i in range(n) if flags[i] & 1}
+
+
+def objects_from_regions(mask, enclosed, min_area, labels, label_map=None):
+    """Reference-literal objects of one frame (sem_seg_server.py:92-133) with the per-contour label
+    histogram taken from the GPU's region table: `enclosed` is fold_region_histograms(...) of the frame.
+    Contours, polygon area and moments come from OpenCV as in the reference.  Hole contours above the
+    area threshold (rare) and frames without a complete table use the polygon fill on `label_map`
+    (callable or array; only touched in those cases)."""
+    import cv2
+    mask = np.ascontiguousarray(mask)
+    contours, hierarchy = cv2.findContours(mask, cv2.RETR_TREE, cv2.CHAIN_APPROX_SIMPLE)
+    objs, w = [], mask.shape[1]
+    segment_img = None
+    for i in range(len(contours)):
+        area = cv2.contourArea(contours[i])
+        if area < min_area:
+            continue
+        counts = None
+        if enclosed is not None:
+            depth, j = 0, hierarchy[0][i][3]
+            while j >= 0:                              # outer contours sit at even depth of the RETR_TREE hierarchy
+                depth, j = depth + 1, hierarchy[0][j][3]
+            if depth % 2 == 0:
+                x, y = contours[i][0][0]               # cv2 starts an outer contour at the region's first pixel
+                counts = enclosed.get(int(y) * w + int(x))
+        if counts is None:
+            if segment_img is None:
+                segment_img = label_map() if callable(label_map) else label_map
+            bx, by, bw, bh = cv2.boundingRect(contours[i])
+            filled = np.zeros((bh, bw), dtype=np.uint8)
+            cv2.drawContours(filled, contours, i, color=255, thickness=-1, offset=(-bx, -by))
+            counts = np.bincount(segment_img[by:by + bh, bx:bx + bw][filled == 255])
+        idx = int(np.argmax(counts))
+        score = int(counts[idx]) / int(counts.sum())
+        m = cv2.moments(contours[i])
+        if not m["m00"]:
+            continue
+        objs.append(SegmentContour(label=labels.get(idx, 0), score=score, area=area,
+                                   centroid=Centroid(cx=int(m["m10"] / m["m00"]), cy=int(m["m01"] / m["m00"]))))
+    return objs
+
+
 def normalise(obj, width, height):
     """(label, score, area, cx, cy) with the reply normalisation of sem_seg_server.py:184-192."""
     return (obj.label, obj.score, min(1.0, obj.area / (width * height)),
