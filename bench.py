@@ -206,6 +206,14 @@ def other_kernels(ssb200, torch):
     assert bool((lab_b.long() == lab_true).all())
     out.append({"kernel": "argmax_stats u8, blobby label maps (batch 64, one batch re-read: L2 holds 1/3 of it)", "us": us,
                 "frames_per_s": b / us * 1e6, "GBps": ALGO_BYTES_PER_FRAME * b / us / 1e3})
+    # reference-literal tail on those label maps (row f1): mask, then the region tables the host reads
+    # instead of filling one polygon per contour
+    mask_b = torch.empty_like(lab_b)
+    us_m = _time_us(torch, lambda i: ssb200.foreground_mask(lab_b, CAM_ROI_H, CAM_ROI_W, cm, out=mask_b), 20)
+    us_r = _time_us(torch, lambda i: ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024), 20)
+    regions = ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024)["count"].float().mean().item()
+    out.append({"kernel": "fg_mask + blob_regions, blobby label maps, ROI 288x513 (batch 64)", "us_fg_mask": us_m,
+                "us_blob_regions": us_r, "frames_per_s": b / (us_m + us_r) * 1e6, "regions_per_frame": regions})
     del qb, field, lab_true
     # config 3 as one unit: 256 camera frames -> K1 -> model input, and the post-process of 256 frames with
     # the 16:9 crop (the class scores are synthetic: the model between the two is not part of the path)

@@ -61,36 +61,72 @@ __device__ __forceinline__ void unite(int *par, int a, int b) {
     }
 }
 
+// A warp walks 32-pixel segments of rows.  Inside a segment every pixel starts out pointing at the first
+// pixel of its horizontal run (ballot of "differs from the pixel on the left", no atomics); what is left
+// for the merge pass are the links a run structure does not imply: a segment's first pixel to the run
+// that continues from the previous segment, and vertical / diagonal links where the pixel on the left
+// has not already made them.
+__device__ __forceinline__ bool segment_of(const BlobParams &p, long long seg, int lane, int *f, int *y, int *x) {
+    const int segs_per_row = (p.roi_w + 31) >> 5;
+    const long long row = seg / segs_per_row;
+    *f = static_cast<int>(row / p.roi_h);
+    *y = static_cast<int>(row - static_cast<long long>(*f) * p.roi_h);
+    *x = static_cast<int>(seg - row * segs_per_row) * 32 + lane;
+    return *x < p.roi_w;
+}
+
 __global__ void __launch_bounds__(kBlobThreads) blob_init_kernel(const BlobParams p) {
     pdl_trigger();
     pdl_wait();
-    const int n = p.roi_h * p.roi_w;
-    const long long total = static_cast<long long>(p.B) * n;
-    for (long long i = blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x; i < total;
-         i += static_cast<long long>(gridDim.x) * kBlobThreads)
-        p.root[i] = static_cast<int>(i % n);
+    const int lane = threadIdx.x & 31, n = p.roi_h * p.roi_w;
+    const long long n_seg = static_cast<long long>(p.B) * p.roi_h * ((p.roi_w + 31) >> 5);
+    const long long warp0 = (blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x) >> 5;
+    const long long n_warps = static_cast<long long>(gridDim.x) * (kBlobThreads >> 5);
+    for (long long seg = warp0; seg < n_seg; seg += n_warps) {
+        int f, y, x;
+        const bool live = segment_of(p, seg, lane, &f, &y, &x);
+        const uint8_t *m = p.mask + static_cast<long long>(f) * p.H * p.W + static_cast<long long>(y) * p.W;
+        const bool fg = live && m[x] != 0;
+        // bit l: lane l starts a run inside this segment (lane 0 always does: its link to the left is made later)
+        const bool starts = live && (lane == 0 || (m[x - 1] != 0) != fg);
+        const unsigned int bits = __ballot_sync(0xffffffffu, starts);
+        if (live) {
+            const int start_lane = 31 - __clz(bits & (0xffffffffu >> (31 - lane)));
+            p.root[static_cast<long long>(f) * n + y * p.roi_w + x] = y * p.roi_w + x - (lane - start_lane);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(kBlobThreads) blob_merge_kernel(const BlobParams p) {
     pdl_trigger();
     pdl_wait();
-    const int n = p.roi_h * p.roi_w;
-    const long long total = static_cast<long long>(p.B) * n;
-    for (long long i = blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x; i < total;
-         i += static_cast<long long>(gridDim.x) * kBlobThreads) {
-        const int f = static_cast<int>(i / n), r = static_cast<int>(i - static_cast<long long>(f) * n);
-        const int y = r / p.roi_w, x = r - y * p.roi_w;
-        const uint8_t *m = p.mask + static_cast<long long>(f) * p.H * p.W;
+    const int lane = threadIdx.x & 31, n = p.roi_h * p.roi_w;
+    const long long n_seg = static_cast<long long>(p.B) * p.roi_h * ((p.roi_w + 31) >> 5);
+    const long long warp0 = (blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x) >> 5;
+    const long long n_warps = static_cast<long long>(gridDim.x) * (kBlobThreads >> 5);
+    for (long long seg = warp0; seg < n_seg; seg += n_warps) {
+        int f, y, x;
+        if (!segment_of(p, seg, lane, &f, &y, &x)) continue;
+        const uint8_t *m = p.mask + static_cast<long long>(f) * p.H * p.W + static_cast<long long>(y) * p.W;
         int *par = p.root + static_cast<long long>(f) * n;
-        const bool fg = m[y * p.W + x] != 0;
-        if (x > 0 && (m[y * p.W + x - 1] != 0) == fg) unite(par, r, r - 1);
-        if (y > 0) {
-            const uint8_t *up = m + (y - 1) * p.W;
-            if ((up[x] != 0) == fg) unite(par, r, r - p.roi_w);
-            if (fg) {   // diagonals connect foreground only
-                if (x > 0 && up[x - 1] != 0) unite(par, r, r - p.roi_w - 1);
-                if (x + 1 < p.roi_w && up[x + 1] != 0) unite(par, r, r - p.roi_w + 1);
-            }
+        const int r = y * p.roi_w + x;
+        const bool fg = m[x] != 0;
+        const bool w_same = x > 0 && (m[x - 1] != 0) == fg;
+        if (lane == 0 && w_same) unite(par, r, r - 1);              // the run continues from the previous segment
+        if (y == 0) continue;
+        const uint8_t *up = m - p.W;
+        const bool n_same = (up[x] != 0) == fg;
+        const bool nw_fg = x > 0 && up[x - 1] != 0, ne_fg = x + 1 < p.roi_w && up[x + 1] != 0;
+        if (n_same) {
+            // implied by the pixel on the left when it, and the pixel above it, are of this kind too
+            const bool nw_same = x > 0 && (up[x - 1] != 0) == fg;
+            if (!(w_same && nw_same)) unite(par, r, r - p.roi_w);
+        } else if (fg) {
+            // diagonals connect foreground only, and only matter when the pixel above is background;
+            // the west / east neighbour makes the link itself when it is foreground (it sits below that pixel)
+            if (nw_fg && !w_same) unite(par, r, r - p.roi_w - 1);
+            const bool e_fg = x + 1 < p.roi_w && m[x + 1] != 0;
+            if (ne_fg && !e_fg) unite(par, r, r - p.roi_w + 1);
         }
     }
 }

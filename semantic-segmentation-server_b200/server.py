@@ -103,6 +103,8 @@ class ArrayCamera:
         return {cv2.CAP_PROP_FRAME_WIDTH: w, cv2.CAP_PROP_FRAME_HEIGHT: h}.get(prop, 0)
 
 
+REGION_ROWS = 256     # rows of the per-frame region table; frames with more regions use the polygon fill
+
 _pool = None
 
 
@@ -132,6 +134,7 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
     cap = _open_camera(camera_idx)
     geom = None
     done = 0
+    staging = hotpath.HostStaging()
     try:
         while cap.isOpened():
             frames = []
@@ -148,23 +151,32 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
             batch = torch.from_numpy(np.stack(frames)).to(dev, non_blocking=True)
             inputs = hotpath.preprocess_frames(batch, geom)                       # :150-161
             logits, scale, zero_point = engine.run_logits(inputs)                 # :162 (model, upstream)
-            if getattr(engine, "layout", "nhwc") == "nchw":                       # :163-170, :102-122
+            nchw = getattr(engine, "layout", "nhwc") == "nchw"
+            if nchw:                                                              # :163-170, :102-122
                 label_maps, stats = hotpath.argmax_stats_nchw(logits, geom.roi_h, geom.roi_w)
             else:
                 label_maps, stats = hotpath.argmax_stats(logits, geom.roi_h, geom.roi_w)
             if mode == "contours":
                 masks = hotpath.foreground_mask(label_maps, geom.roi_h, geom.roi_w)   # :173, :79-85
-                masks_h = masks[:, :geom.roi_h, :geom.roi_w].cpu().numpy()
-                labels_h = label_maps[:, :geom.roi_h, :geom.roi_w].cpu().numpy()
-            else:
-                stats_h = stats.cpu().numpy()
-            if mode == "contours":
+                # :98-111 for every contour at once: region tables instead of one polygon fill per contour
+                tables = hotpath.blob_regions(masks, label_maps, geom.roi_h, geom.roi_w, logits.shape[1 if nchw else 3],
+                                              REGION_ROWS)
+                tables_h = staging.fetch(dict(tables, mask=masks))            # pinned buffers, one wait
+                masks_h = tables_h["mask"][:, :geom.roi_h, :geom.roi_w]
+
+                def contour_tail(i):
+                    enclosed = hotpath.fold_region_histograms(tables_h["count"][i], tables_h["first"][i], tables_h["parent"][i],
+                                                              tables_h["flags"][i], tables_h["hist"][i])
+                    # the label map is only needed for what the table does not cover (large hole contours,
+                    # frames with more regions than table rows): fetched per frame, on demand
+                    return hotpath.objects_from_regions(
+                        masks_h[i], enclosed, segment_centroid_min_area, labels,
+                        label_map=lambda: label_maps[i, :geom.roi_h, :geom.roi_w].cpu().numpy())
                 # OpenCV releases the GIL: the per-frame contour tails of a batch run side by side;
                 # results are consumed in frame order, so the deque looks exactly as in the reference
-                per_frame = list(_contour_pool().map(
-                    lambda i: hotpath.objects_from_contours(masks_h[i], labels_h[i], segment_centroid_min_area, labels),
-                    range(len(frames))))
+                per_frame = list(_contour_pool().map(contour_tail, range(len(frames))))
             else:
+                stats_h = staging.fetch({"stats": stats})["stats"]
                 shift = 0 if logits.dtype == torch.uint8 else hotpath._cabi.F16_FIXED_SHIFT
                 per_frame = [hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, scale,
                                                         zero_point, fixed_shift=shift)[0] for i in range(len(frames))]
