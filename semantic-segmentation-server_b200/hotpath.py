@@ -10,7 +10,10 @@ Names, argument meaning and error behaviour follow the reference where a counter
     foreground_mask                 sem_seg_server.py:173 + 79-85 (device)
     objects_from_stats              sem_seg_server.py:92-133 + 183-192 restated per label
     objects_from_contours           sem_seg_server.py:77-133 + 183-192, reference-literal (cv2 on the
-                                    GPU-made mask; the polygon area/moment step stays on the CPU)
+                                    GPU-made mask; one polygon fill per contour, as the reference does)
+    blob_regions, fold_region_histograms, objects_from_regions
+                                    the same objects with :98-111 read from the GPU's region tables
+                                    (contours, polygon area and moments stay with cv2 on the CPU)
 PyTorch is used for device memory and streams only.
 """
 import collections
