@@ -36,6 +36,13 @@ def main():
     cm = torch.from_numpy(ssb200.create_pascal_label_colormap().astype(np.uint8)).cuda()
     for _ in range(REPS):
         ssb200.foreground_mask(labels, geom.roi_h, geom.roi_w, cm)
+    # K5 on blobby maps (regions of 16x16 cells) and their masks
+    field = torch.randint(1, 21, (64, 33, 33), device="cuda", generator=g)
+    field[torch.rand((64, 33, 33), device="cuda", generator=g) < 0.7] = 0
+    blobby = field.repeat_interleave(16, 1).repeat_interleave(16, 2)[:, :H, :W].to(torch.uint8).contiguous()
+    bmask = ssb200.foreground_mask(blobby, geom.roi_h, geom.roi_w, cm)
+    for _ in range(REPS):
+        ssb200.blob_regions(bmask, blobby, geom.roi_h, geom.roi_w, 21, 1024)
     del q
     # K2+K3 fp16, Cityscapes shape
     h16 = torch.randn((8, 1024, 2048, 19), dtype=torch.float16, device="cuda", generator=g)
