@@ -380,6 +380,39 @@ def test_fg_mask_matches_reference_fixtures(ssb, golden):
         assert not mask[roi_h:].any() and not mask[:, roi_w:].any()
 
 
+@pytest.mark.parametrize("shape,roi", [((3, 513, 513), (288, 513)), ((2, 513, 513), (513, 513)), ((2, 70, 131), (69, 130)),
+                                       ((1, 9, 5), (9, 5)), ((2, 64, 128), (1, 128)), ((1, 200, 300), (200, 1)),
+                                       ((1, 130, 257), (100, 200))])
+def test_fg_mask_random_maps_and_rois(ssb, shape, roi):
+    """Noise (every 3x3 window mixes labels) and blocky maps, strips that straddle the ROI's bottom and right
+    edges, single-row and single-column ROIs."""
+    rng = np.random.default_rng(shape[1] * 7 + roi[0])
+    cm = sp.pascal_colormap().astype(np.uint8)
+    for kind in range(2):
+        if kind == 0:
+            lm = rng.integers(0, 21, shape).astype(np.uint8)
+        else:
+            small = rng.choice([0, 7, 15, 12], size=(shape[0], shape[1] // 6 + 1, shape[2] // 6 + 1))
+            lm = np.kron(small, np.ones((1, 6, 6), int))[:, :shape[1], :shape[2]].astype(np.uint8)
+        mask = ssb.foreground_mask(torch.from_numpy(lm).cuda(), roi[0], roi[1]).cpu().numpy()
+        assert (mask == cport.fg_mask(lm, roi[0], roi[1], cm)).all()
+
+
+def test_fg_mask_colours_outside_the_packed_range(ssb):
+    """Labels >= 64 have colours that are not multiples of 64 (and a caller may pass any colormap): those
+    box sums are recomputed from the colormap bytes."""
+    rng = np.random.default_rng(8)
+    cm = sp.pascal_colormap().astype(np.uint8)
+    lm = rng.integers(0, 256, (2, 120, 140)).astype(np.uint8)
+    lm[1, 30:90, 20:120] = 15                        # a region where only the rim meets such labels
+    mask = ssb.foreground_mask(torch.from_numpy(lm).cuda(), 110, 133).cpu().numpy()
+    assert (mask == cport.fg_mask(lm, 110, 133, cm)).all()
+    odd = rng.integers(0, 256, (256, 3)).astype(np.uint8)      # an arbitrary colormap
+    lm2 = rng.integers(0, 21, (1, 64, 64)).astype(np.uint8)
+    mask2 = ssb.foreground_mask(torch.from_numpy(lm2).cuda(), 64, 64, torch.from_numpy(odd).cuda()).cpu().numpy()
+    assert (mask2 == cport.fg_mask(lm2, 64, 64, odd)).all()
+
+
 def test_reference_literal_objects_from_gpu_mask(ssb, golden):
     """sem_seg_server.py:173-195 reproduced from GPU products: label map (K2) -> mask (GPU) ->
     contours/moments (cv2 on host) -> normalised reply values; bit-exact in FP32."""
