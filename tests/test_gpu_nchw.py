@@ -150,6 +150,24 @@ def test_agrees_with_nhwc_entry_on_transposed_fp16(ssb):
     assert torch.equal(l1, l2) and torch.equal(s1, s2)
 
 
+def test_full_batch_agrees_with_interleaved_kernel_and_invariants(ssb):
+    """Config-2 sized batch (64 x 21 x 513 x 513 fp16, 707 MB): the planar kernel against the interleaved
+    one on the permuted tensor, plus size-independent properties of the statistics."""
+    torch.manual_seed(5)
+    x = torch.randn((64, 21, 513, 513), device="cuda", dtype=torch.float16)
+    labels, stats = ssb.argmax_stats_nchw(x, 288, 513)
+    l2, s2 = ssb.argmax_stats(x.permute(0, 2, 3, 1).contiguous(), 288, 513)
+    torch.cuda.synchronize()
+    assert torch.equal(labels, l2) and torch.equal(stats, s2)
+    n = stats[:, :, 0]
+    assert bool((n.sum(dim=1) == 288 * 513).all())
+    assert int(stats[:, :, 1].sum()) == 64 * 288 * (513 * 512 // 2)           # every column index, 288 times per frame
+    assert int(stats[:, :, 2].sum()) == 64 * 513 * (288 * 287 // 2)
+    want_labels, want_stats = oracle(x[:2].cpu().numpy(), 288, 513)            # and the oracle on two of the frames
+    assert (labels[:2].cpu().numpy() == want_labels).all()
+    assert (stats[:2].cpu().numpy().view(np.uint64) == want_stats).all()
+
+
 def test_argument_errors(ssb):
     x = torch.zeros((1, 21, 8, 8), device="cuda")
     with pytest.raises(ssb._cabi.SsbError):
