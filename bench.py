@@ -235,6 +235,21 @@ def other_kernels(ssb200, torch):
                 "preprocess_frac_of_measured_peak": sector3 / us_k1 / 1e3 / peak,
                 "GBps_sector_effective_both": (sector3 + ALGO_BYTES_PER_FRAME * b) / us / 1e3})
     del cam, rgb3, q3
+    # row f3: camera frames held in pinned host memory -> K1 -> model inputs back in host memory
+    nb = 64
+    cam_h = torch.randint(0, 256, (nb, 1080, 1920, 3), dtype=torch.uint8).pin_memory()
+    rgb_h = torch.empty((nb, H, W, 3), dtype=torch.uint8).pin_memory()
+    ingest = ssb200.IngestPipeline(geom, frames_per_chunk=16, n_slots=3)
+    for _ in range(2):
+        ingest.preprocess(cam_h.numpy(), out=rgb_h.numpy())
+    t0 = time.perf_counter()
+    for _ in range(5):
+        ingest.preprocess(cam_h.numpy(), out=rgb_h.numpy())
+    ing_s = (time.perf_counter() - t0) / 5
+    ingest.close()
+    out.append({"kernel": "ingest: 64 x 1080p frames, pinned host -> K1 -> pinned host (3 streams x 16-frame chunks)",
+                "us": ing_s * 1e6, "frames_per_s": nb / ing_s, "h2d_GBps": nb * 1080 * 1920 * 3 / ing_s / 1e9})
+    del cam_h, rgb_h
     # planar scores left on the GPU by a convolutional head (row f4): fp32 and fp16 [B,21,513,513]
     for dt, nb in ((torch.float32, 32), (torch.float16, 64)):
         pl = [torch.randn((nb, C, H, W), dtype=dt, device="cuda", generator=g) for _ in range(2)]
