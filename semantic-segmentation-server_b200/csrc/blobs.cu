@@ -44,11 +44,25 @@ __device__ __forceinline__ int find_root(const int *par, int a) {
     return a;
 }
 
+// The same walk, halving the path as it goes (every visited node is re-pointed at its grandparent).  The
+// plain stores race with other threads' walks and links, harmlessly: a node only ever gets re-pointed at
+// one of its own ancestors, which keeps it in its tree and keeps parent < child.
+__device__ __forceinline__ int find_root_halving(int *par, int a) {
+    while (true) {
+        const int p = par[a];
+        if (p == a) return a;
+        const int gp = par[p];
+        if (gp == p) return p;
+        par[a] = gp;
+        a = gp;
+    }
+}
+
 // Links the trees of a and b: the larger root goes under the smaller one.
 __device__ __forceinline__ void unite(int *par, int a, int b) {
     while (true) {
-        a = find_root(par, a);
-        b = find_root(par, b);
+        a = find_root_halving(par, a);
+        b = find_root_halving(par, b);
         if (a == b) return;
         if (a < b) {
             const int t = a;
@@ -61,99 +75,98 @@ __device__ __forceinline__ void unite(int *par, int a, int b) {
     }
 }
 
-// A warp walks 32-pixel segments of rows.  Inside a segment every pixel starts out pointing at the first
-// pixel of its horizontal run (ballot of "differs from the pixel on the left", no atomics); what is left
-// for the merge pass are the links a run structure does not imply: a segment's first pixel to the run
-// that continues from the previous segment, and vertical / diagonal links where the pixel on the left
-// has not already made them.
-__device__ __forceinline__ bool segment_of(const BlobParams &p, long long seg, int lane, int *f, int *y, int *x) {
-    const int segs_per_row = (p.roi_w + 31) >> 5;
-    const long long row = seg / segs_per_row;
-    *f = static_cast<int>(row / p.roi_h);
-    *y = static_cast<int>(row - static_cast<long long>(*f) * p.roi_h);
-    *x = static_cast<int>(seg - row * segs_per_row) * 32 + lane;
-    return *x < p.roi_w;
+// Thread mapping of all four kernels: block (32, 8) = 8 warps, warp w of block (bx, by, bz) owns the
+// 32-pixel segment bx of rows 64*by + 8*w .. +7 of frame bz (no index divisions anywhere; one pixel per
+// thread made the kernels bound by the rate at which an SM can start CTAs).
+//
+// Inside a segment every pixel starts out pointing at the first pixel of its horizontal run (ballot of
+// "differs from the pixel on the left", no atomics); what is left for the merge pass are the links a run
+// structure does not imply: a segment's first pixel to the run that continues from the previous segment,
+// and vertical / diagonal links where the pixel on the left has not already made them.
+struct PixelId {
+    int f, y, x, r;
+    bool live;
+};
+constexpr int kBlobRowsPerWarp = 8;
+__device__ __forceinline__ PixelId pixel_of(const BlobParams &p, int k) {
+    PixelId q;
+    q.f = blockIdx.z;
+    q.y = (blockIdx.y * 8 + threadIdx.y) * kBlobRowsPerWarp + k;
+    q.x = blockIdx.x * 32 + threadIdx.x;
+    q.live = q.y < p.roi_h && q.x < p.roi_w;
+    q.r = q.y * p.roi_w + q.x;
+    return q;
 }
 
 __global__ void __launch_bounds__(kBlobThreads) blob_init_kernel(const BlobParams p) {
     pdl_trigger();
     pdl_wait();
-    const int lane = threadIdx.x & 31, n = p.roi_h * p.roi_w;
-    const long long n_seg = static_cast<long long>(p.B) * p.roi_h * ((p.roi_w + 31) >> 5);
-    const long long warp0 = (blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x) >> 5;
-    const long long n_warps = static_cast<long long>(gridDim.x) * (kBlobThreads >> 5);
-    for (long long seg = warp0; seg < n_seg; seg += n_warps) {
-        int f, y, x;
-        const bool live = segment_of(p, seg, lane, &f, &y, &x);
-        const uint8_t *m = p.mask + static_cast<long long>(f) * p.H * p.W + static_cast<long long>(y) * p.W;
-        const bool fg = live && m[x] != 0;
-        // bit l: lane l starts a run inside this segment (lane 0 always does: its link to the left is made later)
-        const bool starts = live && (lane == 0 || (m[x - 1] != 0) != fg);
-        const unsigned int bits = __ballot_sync(0xffffffffu, starts);
-        if (live) {
-            const int start_lane = 31 - __clz(bits & (0xffffffffu >> (31 - lane)));
-            p.root[static_cast<long long>(f) * n + y * p.roi_w + x] = y * p.roi_w + x - (lane - start_lane);
-        }
+    for (int k = 0; k < kBlobRowsPerWarp; ++k) {
+    const PixelId q = pixel_of(p, k);
+    const int lane = threadIdx.x, n = p.roi_h * p.roi_w;
+    const uint8_t *m = p.mask + static_cast<long long>(q.f) * p.H * p.W + static_cast<long long>(q.y) * p.W;
+    const bool fg = q.live && m[q.x] != 0;
+    // bit l: lane l starts a run inside this segment (lane 0 always does: its link to the left is made later)
+    const bool starts = q.live && (lane == 0 || (m[q.x - 1] != 0) != fg);
+    const unsigned int bits = __ballot_sync(0xffffffffu, starts);
+    if (q.live) {
+        const int start_lane = 31 - __clz(bits & (0xffffffffu >> (31 - lane)));
+        p.root[static_cast<long long>(q.f) * n + q.r] = q.r - (lane - start_lane);
+    }
     }
 }
 
 __global__ void __launch_bounds__(kBlobThreads) blob_merge_kernel(const BlobParams p) {
     pdl_trigger();
     pdl_wait();
-    const int lane = threadIdx.x & 31, n = p.roi_h * p.roi_w;
-    const long long n_seg = static_cast<long long>(p.B) * p.roi_h * ((p.roi_w + 31) >> 5);
-    const long long warp0 = (blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x) >> 5;
-    const long long n_warps = static_cast<long long>(gridDim.x) * (kBlobThreads >> 5);
-    for (long long seg = warp0; seg < n_seg; seg += n_warps) {
-        int f, y, x;
-        if (!segment_of(p, seg, lane, &f, &y, &x)) continue;
-        const uint8_t *m = p.mask + static_cast<long long>(f) * p.H * p.W + static_cast<long long>(y) * p.W;
-        int *par = p.root + static_cast<long long>(f) * n;
-        const int r = y * p.roi_w + x;
-        const bool fg = m[x] != 0;
-        const bool w_same = x > 0 && (m[x - 1] != 0) == fg;
-        if (lane == 0 && w_same) unite(par, r, r - 1);              // the run continues from the previous segment
-        if (y == 0) continue;
-        const uint8_t *up = m - p.W;
-        const bool n_same = (up[x] != 0) == fg;
+    for (int k = 0; k < kBlobRowsPerWarp; ++k) {
+    const PixelId q = pixel_of(p, k);
+    if (!q.live) continue;
+    const int lane = threadIdx.x, n = p.roi_h * p.roi_w, x = q.x, r = q.r;
+    const uint8_t *m = p.mask + static_cast<long long>(q.f) * p.H * p.W + static_cast<long long>(q.y) * p.W;
+    int *par = p.root + static_cast<long long>(q.f) * n;
+    const bool fg = m[x] != 0;
+    const bool w_same = x > 0 && (m[x - 1] != 0) == fg;
+    if (lane == 0 && w_same) unite(par, r, r - 1);              // the run continues from the previous segment
+    if (q.y == 0) continue;
+    const uint8_t *up = m - p.W;
+    const bool n_same = (up[x] != 0) == fg;
+    if (n_same) {
+        // implied by the pixel on the left when it, and the pixel above it, are of this kind too
+        const bool nw_same = x > 0 && (up[x - 1] != 0) == fg;
+        if (!(w_same && nw_same)) unite(par, r, r - p.roi_w);
+    } else if (fg) {
+        // diagonals connect foreground only, and only matter when the pixel above is background;
+        // the west / east neighbour makes the link itself when it is foreground (it sits below that pixel)
         const bool nw_fg = x > 0 && up[x - 1] != 0, ne_fg = x + 1 < p.roi_w && up[x + 1] != 0;
-        if (n_same) {
-            // implied by the pixel on the left when it, and the pixel above it, are of this kind too
-            const bool nw_same = x > 0 && (up[x - 1] != 0) == fg;
-            if (!(w_same && nw_same)) unite(par, r, r - p.roi_w);
-        } else if (fg) {
-            // diagonals connect foreground only, and only matter when the pixel above is background;
-            // the west / east neighbour makes the link itself when it is foreground (it sits below that pixel)
-            if (nw_fg && !w_same) unite(par, r, r - p.roi_w - 1);
-            const bool e_fg = x + 1 < p.roi_w && m[x + 1] != 0;
-            if (ne_fg && !e_fg) unite(par, r, r - p.roi_w + 1);
-        }
+        if (nw_fg && !w_same) unite(par, r, r - p.roi_w - 1);
+        const bool e_fg = x + 1 < p.roi_w && m[x + 1] != 0;
+        if (ne_fg && !e_fg) unite(par, r, r - p.roi_w + 1);
+    }
     }
 }
 
 __global__ void __launch_bounds__(kBlobThreads) blob_flatten_kernel(const BlobParams p) {
     pdl_trigger();
     pdl_wait();
-    const int n = p.roi_h * p.roi_w;
-    const long long total = static_cast<long long>(p.B) * n;
-    for (long long i = blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x; i < total;
-         i += static_cast<long long>(gridDim.x) * kBlobThreads) {
-        const int f = static_cast<int>(i / n), r = static_cast<int>(i - static_cast<long long>(f) * n);
-        int *par = p.root + static_cast<long long>(f) * n;
-        const int root = find_root(par, r);
-        // Writing the root shortens other threads' walks and never breaks them: par[r] still points at
-        // an ancestor.  A root keeps par[root] == root.
-        par[r] = root;
-        if (root == r) {
-            const int s = atomicAdd(&p.count[f], 1);
-            p.slot[i] = s;
-            if (s < p.max_regions) {
-                const int y = r / p.roi_w, x = r - y * p.roi_w;
-                const bool fg = p.mask[static_cast<long long>(f) * p.H * p.W + y * p.W + x] != 0;
-                p.first[static_cast<long long>(f) * p.max_regions + s] = r;
-                p.flags[static_cast<long long>(f) * p.max_regions + s] = fg ? 1 : 0;
-            }
+    for (int k = 0; k < kBlobRowsPerWarp; ++k) {
+    const PixelId q = pixel_of(p, k);
+    if (!q.live) continue;
+    const int n = p.roi_h * p.roi_w, r = q.r;
+    int *par = p.root + static_cast<long long>(q.f) * n;
+    const int root = find_root_halving(par, r);
+    // Writing the root shortens other threads' walks and never breaks them: par[r] still points at an
+    // ancestor.  A root keeps par[root] == root.
+    par[r] = root;
+    if (root == r) {
+        const int s = atomicAdd(&p.count[q.f], 1);
+        p.slot[static_cast<long long>(q.f) * n + r] = s;
+        if (s < p.max_regions) {
+            const bool fg = p.mask[static_cast<long long>(q.f) * p.H * p.W + static_cast<long long>(q.y) * p.W + q.x] != 0;
+            p.first[static_cast<long long>(q.f) * p.max_regions + s] = r;
+            p.flags[static_cast<long long>(q.f) * p.max_regions + s] = fg ? 1 : 0;
         }
+    }
     }
 }
 
@@ -162,42 +175,31 @@ __global__ void __launch_bounds__(kBlobThreads) blob_flatten_kernel(const BlobPa
 __global__ void __launch_bounds__(kBlobThreads) blob_tables_kernel(const BlobParams p) {
     pdl_trigger();
     pdl_wait();
-    const int n = p.roi_h * p.roi_w;
-    const long long total = static_cast<long long>(p.B) * n;
-    const int lane = threadIdx.x & 31;
-    // whole warps stay in the loop (shuffles below): the bound is rounded up to a multiple of 32
-    const long long total32 = (total + 31) / 32 * 32;
-    for (long long i = blockIdx.x * static_cast<long long>(kBlobThreads) + threadIdx.x; i < total32;
-         i += static_cast<long long>(gridDim.x) * kBlobThreads) {
-        const bool live = i < total;
-        int f = 0, r = 0, root = 0, s = 0x7fffffff, lab = 0;
-        bool fg = false, edge = false;
-        if (live) {
-            f = static_cast<int>(i / n);
-            r = static_cast<int>(i - static_cast<long long>(f) * n);
-            const int *par = p.root + static_cast<long long>(f) * n;
-            root = find_root(par, r);
-            s = p.slot[static_cast<long long>(f) * n + root];
-            const int y = r / p.roi_w, x = r - y * p.roi_w;
-            const long long px = static_cast<long long>(f) * p.H * p.W + y * p.W + x;
-            lab = p.labels[px];
-            fg = p.mask[px] != 0;
-            edge = x == 0 || y == 0 || x == p.roi_w - 1 || y == p.roi_h - 1;
-            if (r == root && s < p.max_regions) {
-                // the region that encloses this one owns the pixel left of its first pixel
-                int par_first = -1;
-                if (x > 0) par_first = find_root(par, r - 1);
-                p.parent[static_cast<long long>(f) * p.max_regions + s] = par_first;
-            }
+    for (int k = 0; k < kBlobRowsPerWarp; ++k) {   // warp-uniform: the shuffles below see all 32 lanes
+    const PixelId q = pixel_of(p, k);
+    const int n = p.roi_h * p.roi_w, lane = threadIdx.x, f = q.f;
+    int s = 0x7fffffff, lab = 0;
+    bool fg = false, edge = false;
+    if (q.live) {
+        const int *par = p.root + static_cast<long long>(f) * n;
+        const int root = find_root(par, q.r);
+        s = p.slot[static_cast<long long>(f) * n + root];
+        const long long px = static_cast<long long>(f) * p.H * p.W + static_cast<long long>(q.y) * p.W + q.x;
+        lab = p.labels[px];
+        fg = p.mask[px] != 0;
+        edge = q.x == 0 || q.y == 0 || q.x == p.roi_w - 1 || q.y == p.roi_h - 1;
+        if (q.r == root && s < p.max_regions) {
+            // the region that encloses this one owns the pixel left of its first pixel
+            p.parent[static_cast<long long>(f) * p.max_regions + s] = q.x > 0 ? find_root(par, q.r - 1) : -1;
         }
-        const bool counted = live && s < p.max_regions && lab < p.C;
-        // one atomic per distinct (frame, region, label) in the warp
-        const unsigned long long key = counted ? ((static_cast<unsigned long long>(f) << 40) | (static_cast<unsigned long long>(s) << 8) | lab)
-                                               : ~0ull - lane;
-        const unsigned int peers = __match_any_sync(0xffffffffu, key);
-        if (counted && lane == __ffs(peers) - 1)
-            atomicAdd(&p.hist[(static_cast<long long>(f) * p.max_regions + s) * p.C + lab], __popc(peers));
-        if (counted && edge && !fg) atomicOr(&p.flags[static_cast<long long>(f) * p.max_regions + s], 2);
+    }
+    const bool counted = q.live && s < p.max_regions && lab < p.C;
+    // one atomic per distinct (region, label) in the warp (a warp is 32 consecutive pixels of one row)
+    const unsigned int key = counted ? (static_cast<unsigned int>(s) << 8) | static_cast<unsigned int>(lab) : 0xffffffffu - lane;
+    const unsigned int peers = __match_any_sync(0xffffffffu, key);
+    if (counted && lane == __ffs(peers) - 1)
+        atomicAdd(&p.hist[(static_cast<long long>(f) * p.max_regions + s) * p.C + lab], __popc(peers));
+    if (counted && edge && !fg) atomicOr(&p.flags[static_cast<long long>(f) * p.max_regions + s], 2);
     }
 }
 
@@ -233,14 +235,12 @@ extern "C" int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, i
     p.count = count; p.first = first; p.parent = parent; p.flags = flags; p.hist = hist;
     SSB_CUDA_TRY(cudaMemsetAsync(count, 0, sizeof(int) * B, st));
     SSB_CUDA_TRY(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * static_cast<size_t>(B) * max_regions * C, st));
-    DeviceInfo di;
-    if (int rc = device_info(&di)) return rc;
-    long long blocks = (static_cast<long long>(n) + kBlobThreads - 1) / kBlobThreads;
-    const long long cap = static_cast<long long>(di.sm_count) * 16;
-    const dim3 grid(static_cast<unsigned>(blocks < cap ? blocks : cap));
-    SSB_CUDA_TRY(launch_pdl(blob_init_kernel, grid, dim3(kBlobThreads), 0, st, p));
-    SSB_CUDA_TRY(launch_pdl(blob_merge_kernel, grid, dim3(kBlobThreads), 0, st, p));
-    SSB_CUDA_TRY(launch_pdl(blob_flatten_kernel, grid, dim3(kBlobThreads), 0, st, p));
-    SSB_CUDA_TRY(launch_pdl(blob_tables_kernel, grid, dim3(kBlobThreads), 0, st, p));
+    constexpr int kRowsPerCta = 8 * kBlobRowsPerWarp;
+    if (B > 65535 || (roi_h + kRowsPerCta - 1) / kRowsPerCta > 65535) return fail(SSB_ERR_LIMIT, "B and roi_h/64 must be <= 65535");
+    const dim3 grid((roi_w + 31) / 32, (roi_h + kRowsPerCta - 1) / kRowsPerCta, B), block(32, 8);
+    SSB_CUDA_TRY(launch_pdl(blob_init_kernel, grid, block, 0, st, p));
+    SSB_CUDA_TRY(launch_pdl(blob_merge_kernel, grid, block, 0, st, p));
+    SSB_CUDA_TRY(launch_pdl(blob_flatten_kernel, grid, block, 0, st, p));
+    SSB_CUDA_TRY(launch_pdl(blob_tables_kernel, grid, block, 0, st, p));
     return SSB_OK;
 }

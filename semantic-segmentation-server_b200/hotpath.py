@@ -182,13 +182,24 @@ def argmax_stats_nchw(logits, roi_h=None, roi_w=None, labels=None, stats=None, w
     return (labels if want_labels else None), stats
 
 
+_COLORMAPS = {}
+
+
+def _pascal_colormap_on(device):
+    """The PASCAL colormap as a [256,3] u8 device tensor, uploaded once per device."""
+    key = str(device)
+    if key not in _COLORMAPS:
+        _COLORMAPS[key] = torch.from_numpy(create_pascal_label_colormap().astype(np.uint8)).to(device)
+    return _COLORMAPS[key]
+
+
 def foreground_mask(labels, roi_h, roi_w, colormap_dev=None, out=None, stream=None):
     """[B,H,W] u8 label maps (device) -> [B,H,W] u8 mask, 255 where the reference's
     blur/gray/threshold stage (sem_seg_server.py:173,79-85) is foreground inside the ROI."""
     _require_cuda(labels, "labels")
     b, h, w = labels.shape
     if colormap_dev is None:
-        colormap_dev = torch.from_numpy(create_pascal_label_colormap().astype(np.uint8)).to(labels.device)
+        colormap_dev = _pascal_colormap_on(labels.device)
     if out is None:
         out = torch.empty_like(labels)
     with torch.cuda.device(labels.device):
