@@ -135,6 +135,7 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
     geom = None
     done = 0
     staging = hotpath.HostStaging()
+    pinned_frames = None
     try:
         while cap.isOpened():
             frames = []
@@ -148,7 +149,13 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
             cam_h, cam_w = frames[0].shape[:2]
             if geom is None or (geom.cam_w, geom.cam_h) != (cam_w, cam_h):
                 geom = hotpath.FrameGeometry(cam_w, cam_h, width, height, keep_aspect_ratio)
-            batch = torch.from_numpy(np.stack(frames)).to(dev, non_blocking=True)
+            # frames are gathered straight into a pinned buffer (one host copy, then a DMA transfer); every
+            # batch ends with a synchronising read-back, so the buffer is free again by the next one
+            if pinned_frames is None or pinned_frames.shape[1:] != (cam_h, cam_w, 3):
+                pinned_frames = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8).pin_memory()
+            for i, f in enumerate(frames):
+                pinned_frames[i].copy_(torch.from_numpy(np.ascontiguousarray(f)))
+            batch = pinned_frames[:len(frames)].to(dev, non_blocking=True)
             inputs = hotpath.preprocess_frames(batch, geom)                       # :150-161
             logits, scale, zero_point = engine.run_logits(inputs)                 # :162 (model, upstream)
             nchw = getattr(engine, "layout", "nhwc") == "nchw"
