@@ -280,6 +280,16 @@ def test_f16_shapes(ssb, shape):
 
 
 # ---- K1 pre-process ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(200, 8, 8, 19), (64, 3, 4, 21), (7, 4000, 4, 19), (5, 1, 3000, 21),
+                                   (600, 5, 5, 19), (3, 2, 1025, 21)])
+def test_f16_extreme_geometries_on_the_streaming_path(ssb, shape):
+    """The fp16 codec through the same frame bookkeeping: frames much smaller than a tile, very narrow
+    and very wide rows, ROI cut both ways."""
+    h = np.random.default_rng(sum(shape) + 1).standard_normal(shape, dtype=np.float32).astype(np.float16)
+    check_vs_oracle(ssb, h)
+    check_vs_oracle(ssb, h, max(1, shape[1] - 1), max(1, shape[2] // 2))
+
+
 def gpu_preprocess(ssb, frames_np, W, H, keep=True):
     b, ch, cw, _ = frames_np.shape
     geom = ssb.FrameGeometry(cw, ch, W, H, keep)
