@@ -175,11 +175,15 @@ SSB_API int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int roi_h
  *                of `first`; -1 when `first` is in column 0
  *   flags        [B][max_regions] bit 0: foreground region; bit 1: background region touching the ROI
  *                border (not a hole: it is the outside)
- *   hist         [B][max_regions][C] u32 label histogram of the region's own pixels */
+ *   hist         [B][max_regions][C] u32 label histogram of the region's own pixels
+ *   ring         [B][max_regions][C] u32 or NULL: for a hole (background region not touching the border), the
+ *                label histogram of the enclosing foreground region's pixels that are 4-adjacent to it --
+ *                the pixels OpenCV's hole contour runs through.  What drawContours fills for a hole contour
+ *                is the hole, everything nested in it, and this ring. */
 SSB_API size_t ssb_blob_regions_scratch_bytes(int B, int roi_h, int roi_w);
 SSB_API int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, int B, int H, int W, int roi_h, int roi_w,
                         int C, int max_regions, void *scratch, int32_t *count, int32_t *first, int32_t *parent,
-                        int32_t *flags, uint32_t *hist, void *stream);
+                        int32_t *flags, uint32_t *hist, uint32_t *ring, void *stream);
 
 /* Host-buffer convenience for callers that hold frames/logits in host memory (the reference's
  * situation: cap.read() and engine.run_inference both return host arrays).

@@ -34,7 +34,7 @@ SIGNATURES = {
                                 _c_void_p]),
     "ssb_blob_regions_scratch_bytes": (ctypes.c_size_t, [_c_int, _c_int, _c_int]),
     "ssb_blob_regions_u8": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
-                                     _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p]),
+                                     _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p]),
     "ssb_pipeline_create": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),
     "ssb_pipeline_destroy": (_c_int, [_c_void_p]),
     "ssb_pipeline_create_ingest": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),

@@ -10,7 +10,9 @@
 // region's own label histogram and its enclosing region ("parent"), the host adds up a contour's
 // histogram by folding children into parents (hotpath.objects_from_regions).  Regions are named by
 // their first pixel in raster order -- the point cv2 starts an outer contour at -- and the parent of a
-// region is the region of the pixel left of that first pixel.
+// region is the region of the pixel left of that first pixel.  A HOLE contour runs through the pixels of
+// the enclosing region that are 4-adjacent to the hole: it encloses the hole, what is nested in it, and
+// that ring, whose label histogram is the `ring` row of the hole.
 //
 // Labelling: union-find over the ROI with atomicMin links (larger root under smaller, so a region's root
 // IS its first pixel): init, merge (west / north-west / north / north-east for foreground, west / north
@@ -33,6 +35,7 @@ struct BlobParams {
     int *parent;             // [B][max_regions] first pixel of the enclosing region, -1 = none (first pixel in column 0)
     int *flags;              // [B][max_regions] bit 0: foreground region, bit 1: touches the ROI border
     unsigned int *hist;      // [B][max_regions][C]
+    unsigned int *ring;      // [B][max_regions][C] or null: for a hole, labels of the enclosing region's pixels that touch it
 };
 
 __device__ __forceinline__ int find_root(const int *par, int a) {
@@ -200,6 +203,30 @@ __global__ void __launch_bounds__(kBlobThreads) blob_tables_kernel(const BlobPar
     if (counted && lane == __ffs(peers) - 1)
         atomicAdd(&p.hist[(static_cast<long long>(f) * p.max_regions + s) * p.C + lab], __popc(peers));
     if (counted && edge && !fg) atomicOr(&p.flags[static_cast<long long>(f) * p.max_regions + s], 2);
+    // Hole contours run through the pixels of the ENCLOSING foreground region that are 4-adjacent to the
+    // hole (not through islands inside the hole): such a pixel adds its label to the hole's ring row.
+    if (p.ring && q.live && fg && lab < p.C) {
+        const int *par = p.root + static_cast<long long>(f) * n;
+        const uint8_t *m = p.mask + static_cast<long long>(f) * p.H * p.W + static_cast<long long>(q.y) * p.W;
+        const int mine = find_root(par, q.r);
+        int seen[4], n_seen = 0;
+        const int dr[4] = {-1, 1, -p.roi_w, p.roi_w};
+        const bool ok[4] = {q.x > 0 && m[q.x - 1] == 0, q.x + 1 < p.roi_w && m[q.x + 1] == 0,
+                            q.y > 0 && m[q.x - p.W] == 0, q.y + 1 < p.roi_h && m[q.x + p.W] == 0};
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+            if (!ok[d]) continue;
+            const int g = find_root(par, q.r + dr[d]);          // the hole's first pixel
+            bool dup = false;
+            for (int e = 0; e < n_seen; ++e) dup |= seen[e] == g;
+            if (dup) continue;
+            seen[n_seen++] = g;
+            if (g % p.roi_w == 0) continue;                     // column 0: touches the border, not a hole
+            if (find_root(par, g - 1) != mine) continue;        // this pixel belongs to an island inside the hole
+            const int sg = p.slot[static_cast<long long>(f) * n + g];
+            if (sg < p.max_regions) atomicAdd(&p.ring[(static_cast<long long>(f) * p.max_regions + sg) * p.C + lab], 1u);
+        }
+    }
     }
 }
 
@@ -213,7 +240,7 @@ extern "C" size_t ssb_blob_regions_scratch_bytes(int B, int roi_h, int roi_w) {
 
 extern "C" int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, int B, int H, int W, int roi_h, int roi_w,
                                    int C, int max_regions, void *scratch, int32_t *count, int32_t *first,
-                                   int32_t *parent, int32_t *flags, uint32_t *hist, void *stream) {
+                                   int32_t *parent, int32_t *flags, uint32_t *hist, uint32_t *ring, void *stream) {
     using namespace ssb;
     if (B < 0 || H <= 0 || W <= 0) return fail(SSB_ERR_BAD_SHAPE, "bad shape B=%d H=%d W=%d", B, H, W);
     if (roi_h < 1 || roi_h > H || roi_w < 1 || roi_w > W)
@@ -232,9 +259,10 @@ extern "C" int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, i
     p.B = B; p.H = H; p.W = W; p.roi_h = roi_h; p.roi_w = roi_w; p.C = C; p.max_regions = max_regions;
     p.root = static_cast<int *>(scratch);
     p.slot = p.root + n;
-    p.count = count; p.first = first; p.parent = parent; p.flags = flags; p.hist = hist;
+    p.count = count; p.first = first; p.parent = parent; p.flags = flags; p.hist = hist; p.ring = ring;
     SSB_CUDA_TRY(cudaMemsetAsync(count, 0, sizeof(int) * B, st));
     SSB_CUDA_TRY(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * static_cast<size_t>(B) * max_regions * C, st));
+    if (ring) SSB_CUDA_TRY(cudaMemsetAsync(ring, 0, sizeof(uint32_t) * static_cast<size_t>(B) * max_regions * C, st));
     constexpr int kRowsPerCta = 8 * kBlobRowsPerWarp;
     if (B > 65535 || (roi_h + kRowsPerCta - 1) / kRowsPerCta > 65535) return fail(SSB_ERR_LIMIT, "B and roi_h/64 must be <= 65535");
     const dim3 grid((roi_w + 31) / 32, (roi_h + kRowsPerCta - 1) / kRowsPerCta, B), block(32, 8);

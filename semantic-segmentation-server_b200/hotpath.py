@@ -289,8 +289,8 @@ class HostStaging:
 
 def blob_regions(masks, label_maps, roi_h, roi_w, num_classes=21, max_regions=256, stream=None):
     """[B,H,W] u8 masks + label maps (device) -> region tables of every frame's ROI, as a dict of device
-    tensors: count [B], first / parent / flags [B,R] int32, hist [B,R,num_classes] int32 (C-ABI:
-    ssb_blob_regions_u8).  Copy them to the host and hand one frame's rows to objects_from_regions."""
+    tensors: count [B], first / parent / flags [B,R] int32, hist and ring [B,R,num_classes] int32 (C-ABI:
+    ssb_blob_regions_u8).  Copy them to the host and hand one frame's rows to fold_region_histograms."""
     _require_cuda(masks, "masks")
     _require_cuda(label_maps, "label_maps")
     b, h, w = masks.shape
@@ -300,42 +300,69 @@ def blob_regions(masks, label_maps, roi_h, roi_w, num_classes=21, max_regions=25
          "first": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
          "parent": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
          "flags": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
-         "hist": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev)}
+         "hist": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev),
+         "ring": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev)}
     with torch.cuda.device(dev):
         _cabi.check(_cabi.lib.ssb_blob_regions_u8(
             masks.data_ptr(), label_maps.data_ptr(), b, h, w, roi_h, roi_w, num_classes, max_regions, scratch.data_ptr(),
             t["count"].data_ptr(), t["first"].data_ptr(), t["parent"].data_ptr(), t["flags"].data_ptr(),
-            t["hist"].data_ptr(), _stream_ptr(stream)))
+            t["hist"].data_ptr(), t["ring"].data_ptr(), _stream_ptr(stream)))
     return t
 
 
-def fold_region_histograms(count, first, parent, flags, hist):
-    """One frame's region table (host numpy) -> {first pixel of a foreground region: label histogram of
-    everything its outer contour encloses} -- the region itself, its holes, and whatever is nested in
-    them; None if the table is incomplete (count > rows).  A region's children all have larger first
-    pixels than it, so one pass in descending order of first pixel folds every subtree."""
+class EnclosedHistograms(dict):
+    """{first pixel of a foreground region: label histogram of everything its outer contour encloses};
+    `.holes` is the same for hole contours, keyed by the first pixel of the hole."""
+    holes = {}
+
+
+def fold_region_histograms(count, first, parent, flags, hist, ring=None):
+    """One frame's region table (host numpy) -> EnclosedHistograms, or None if the table is incomplete
+    (count > rows).  An outer contour encloses its region, the region's holes and whatever is nested in
+    them; a hole contour encloses the hole, what is nested in it, and the ring of the surrounding region's
+    pixels it runs through (`ring`; without it `.holes` stays empty).  A region's children all have larger
+    first pixels than it, so one pass in descending order of first pixel folds every subtree."""
     n = int(count)
     if n > first.shape[0]:
         return None
     first, parent, flags = first[:n], parent[:n], flags[:n]
     enc = hist[:n].astype(np.int64)
     row_of = {int(p): i for i, p in enumerate(first)}
+    outside = (flags & 3) == 2                         # background touching the ROI border
     for i in np.argsort(-first):
-        is_fg, outside = flags[i] & 1, (flags[i] & 2) and not (flags[i] & 1)
-        if outside or parent[i] < 0:
+        if outside[i] or parent[i] < 0:
             continue                                   # the outside, or a region in column 0: nothing encloses it
         j = row_of[int(parent[i])]
-        if (flags[j] & 2) and not (flags[j] & 1):
+        if outside[j]:
             continue                                   # enclosed by the outside only
         enc[j] += enc[i]
-    return {int(first[i]): enc[i] for i in range(n) if flags[i] & 1}
+    out = EnclosedHistograms((int(first[i]), enc[i]) for i in range(n) if flags[i] & 1)
+    out.holes = {}
+    if ring is not None:
+        out.holes = {int(first[i]): enc[i] + ring[i] for i in range(n) if not (flags[i] & 1) and not outside[i]}
+    return out
+
+
+def hole_first_pixel(contour, mask):
+    """First pixel (raster order, y*w + x) of the hole a hole contour of `mask` goes around.  The contour
+    runs through the foreground pixels 4-adjacent to the hole, so its top row is one above the hole's, and
+    a background pixel directly below a contour pixel of that row can only belong to this hole."""
+    pts = contour[:, 0, :]
+    y_top = int(pts[:, 1].min())
+    nxt = np.roll(pts, -1, axis=0)
+    on = pts[:, 1] == y_top
+    xs = set(int(x) for x in pts[on, 0])
+    for a, b in zip(pts[on & (nxt[:, 1] == y_top), 0], nxt[on & (nxt[:, 1] == y_top), 0]):
+        xs.update(range(int(min(a, b)), int(max(a, b)) + 1))     # CHAIN_APPROX_SIMPLE keeps only a run's end points
+    below = [x for x in sorted(xs) if mask[y_top + 1, x] == 0]
+    return (y_top + 1) * mask.shape[1] + below[0] if below else None
 
 
 def objects_from_regions(mask, enclosed, min_area, labels, label_map=None):
     """Reference-literal objects of one frame (sem_seg_server.py:92-133) with the per-contour label
     histogram taken from the GPU's region table: `enclosed` is fold_region_histograms(...) of the frame.
-    Contours, polygon area and moments come from OpenCV as in the reference.  Hole contours above the
-    area threshold (rare) and frames without a complete table use the polygon fill on `label_map`
+    Contours, polygon area and moments come from OpenCV as in the reference.  Frames without a complete
+    table (and hole contours when the table has no ring rows) use the polygon fill on `label_map`
     (callable or array; only touched in those cases)."""
     import cv2
     mask = np.ascontiguousarray(mask)
@@ -354,6 +381,8 @@ def objects_from_regions(mask, enclosed, min_area, labels, label_map=None):
             if depth % 2 == 0:
                 x, y = contours[i][0][0]               # cv2 starts an outer contour at the region's first pixel
                 counts = enclosed.get(int(y) * w + int(x))
+            elif enclosed.holes:
+                counts = enclosed.holes.get(hole_first_pixel(contours[i], mask))
         if counts is None:
             if segment_img is None:
                 segment_img = label_map() if callable(label_map) else label_map

@@ -173,9 +173,8 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
 
                 def contour_tail(i):
                     enclosed = hotpath.fold_region_histograms(tables_h["count"][i], tables_h["first"][i], tables_h["parent"][i],
-                                                              tables_h["flags"][i], tables_h["hist"][i])
-                    # the label map is only needed for what the table does not cover (large hole contours,
-                    # frames with more regions than table rows): fetched per frame, on demand
+                                                              tables_h["flags"][i], tables_h["hist"][i], tables_h["ring"][i])
+                    # the label map is only needed for frames with more regions than table rows: fetched on demand
                     return hotpath.objects_from_regions(
                         masks_h[i], enclosed, segment_centroid_min_area, labels,
                         label_map=lambda: label_maps[i, :geom.roi_h, :geom.roi_w].cpu().numpy())

@@ -19,19 +19,25 @@ def scipy_table(mask, lab, num_classes=21):
     idx = np.arange(h * w).reshape(h, w)
     rows = []
     region_of = np.empty((h, w), np.int64)          # pixel -> first pixel of its region
-    for is_fg, (lbl, n) in ((1, ndimage.label(fg, S8)), (0, ndimage.label(~fg, S4))):
+    lf, nf = ndimage.label(fg, S8)
+    for is_fg, (lbl, n) in ((1, (lf, nf)), (0, ndimage.label(~fg, S4))):
         for k in range(1, n + 1):
             m = lbl == k
             first = int(idx[m].min())
             region_of[m] = first
             touch = (not is_fg) and bool(m[0].any() or m[-1].any() or m[:, 0].any() or m[:, -1].any())
-            rows.append((first, is_fg | (2 if touch else 0), np.bincount(lab[m], minlength=num_classes)))
+            ring = np.zeros(num_classes, np.int64)
+            if not is_fg and not touch:
+                y0, x0 = divmod(first, w)            # a hole: the enclosing region owns the pixel left of its first pixel
+                ring = np.bincount(lab[ndimage.binary_dilation(m, S4) & (lf == lf[y0, x0 - 1])], minlength=num_classes)
+            rows.append((first, is_fg | (2 if touch else 0), np.bincount(lab[m], minlength=num_classes), ring))
     rows.sort(key=lambda r: r[0])
     first = np.array([r[0] for r in rows], np.int32)
     flags = np.array([r[1] for r in rows], np.int32)
     hist = np.array([r[2] for r in rows], np.int32).reshape(len(rows), num_classes)
+    ring = np.array([r[3] for r in rows], np.int32).reshape(len(rows), num_classes)
     parent = np.array([-1 if f % w == 0 else region_of.flat[f - 1] for f in first], np.int32)
-    return len(rows), first, parent, flags, hist
+    return len(rows), first, parent, flags, hist, ring
 
 
 def random_label_map(rng, t):
@@ -67,20 +73,27 @@ def test_objects_from_region_tables_equal_the_polygon_fill_path():
     every contour (also hole contours, which take the fill path inside) is compared."""
     import ssb200
     rng = np.random.default_rng(4)
-    n_outer = 0
+    n_outer = n_holes = 0
+
+    def no_label_map():
+        raise AssertionError("the tables cover every contour: the label map must not be needed")
     for t in range(120):
         mask, lab = random_label_map(rng, t)
-        count, first, parent, flags, hist = scipy_table(mask, lab)
-        enclosed = ssb200.fold_region_histograms(count, first, parent, flags, hist)
+        count, first, parent, flags, hist, ring = scipy_table(mask, lab)
+        enclosed = ssb200.fold_region_histograms(count, first, parent, flags, hist, ring)
         n_outer += len(enclosed)
-        got = ssb200.objects_from_regions(mask, enclosed, 0.0, NAMES, label_map=lab)
+        n_holes += len(enclosed.holes)
         want = ssb200.objects_from_contours(mask, lab, 0.0, NAMES)
-        assert same_objects(got, want), t
+        assert same_objects(ssb200.objects_from_regions(mask, enclosed, 0.0, NAMES, label_map=no_label_map), want), t
+        # without ring rows hole contours take the polygon fill, with the same result
+        no_ring = ssb200.fold_region_histograms(count, first, parent, flags, hist)
+        assert same_objects(ssb200.objects_from_regions(mask, no_ring, 0.0, NAMES, label_map=lab), want), t
         # rows in any order (the kernel hands out rows with an atomic counter)
         perm = rng.permutation(count)
-        enclosed2 = ssb200.fold_region_histograms(count, first[perm], parent[perm], flags[perm], hist[perm])
+        enclosed2 = ssb200.fold_region_histograms(count, first[perm], parent[perm], flags[perm], hist[perm], ring[perm])
         assert all((enclosed[k] == enclosed2[k]).all() for k in enclosed)
-    assert n_outer > 500
+        assert all((enclosed.holes[k] == enclosed2.holes[k]).all() for k in enclosed.holes)
+    assert n_outer > 500 and n_holes > 2000
 
 
 def test_incomplete_table_falls_back_to_the_fill(golden):
@@ -91,7 +104,7 @@ def test_incomplete_table_falls_back_to_the_fill(golden):
     geom = ssb200.FrameGeometry(cw, ch, W, H)
     lab = np.ascontiguousarray(g[name + "_label_map"][:geom.roi_h, :geom.roi_w]).astype(np.uint8)
     mask = sp.foreground_mask(lab)
-    count, first, parent, flags, hist = scipy_table(mask, lab)
+    count, first, parent, flags, hist, ring = scipy_table(mask, lab)
     assert count >= 2
     assert ssb200.fold_region_histograms(count, first[:1], parent[:1], flags[:1], hist[:1]) is None
     fetched = []
@@ -129,13 +142,15 @@ def test_gpu_region_tables_match_scipy_labelling():
         labs[:, :, :] = np.where(labs < 21, labs, 0)
         t = gpu_tables(ssb200, masks, labs, roi_h, roi_w, 8192)
         for b in range(8):
-            count, first, parent, flags, hist = scipy_table(masks[b, :roi_h, :roi_w], labs[b, :roi_h, :roi_w])
+            count, first, parent, flags, hist, ring = scipy_table(masks[b, :roi_h, :roi_w], labs[b, :roi_h, :roi_w])
             assert t["count"][b] == count
             order = np.argsort(t["first"][b, :count])
             assert (t["first"][b, :count][order] == first).all()
             assert (t["parent"][b, :count][order] == parent).all()
             assert (t["flags"][b, :count][order] == flags).all()
             assert (t["hist"][b, :count][order] == hist).all()
+            holes = (flags & 3) == 0                     # ring rows are defined for holes only
+            assert (t["ring"][b, :count][order][holes] == ring[holes]).all()
 
 
 @pytest.mark.gpu
@@ -158,7 +173,7 @@ def test_gpu_regions_reproduce_reference_objects(golden):
         t = ssb200.blob_regions(mask, lm, geom.roi_h, geom.roi_w, 21, 256)
         torch.cuda.synchronize()
         th = {k: v.cpu().numpy()[0] for k, v in t.items()}
-        enclosed = ssb200.fold_region_histograms(th["count"], th["first"], th["parent"], th["flags"], th["hist"])
+        enclosed = ssb200.fold_region_histograms(th["count"], th["first"], th["parent"], th["flags"], th["hist"], th["ring"])
         mask_h = mask[0, :geom.roi_h, :geom.roi_w].cpu().numpy()
         lab_h = lm[0, :geom.roi_h, :geom.roi_w].cpu().numpy()
         objs = ssb200.objects_from_regions(mask_h, enclosed, float(g[name + "_min_area_ratio"]) * W * H, names,
@@ -168,6 +183,41 @@ def test_gpu_regions_reproduce_reference_objects(golden):
         assert (vals[::-1] == g[name + "_obj_vals"]).all(), name
         checked += len(objs)
     assert checked >= 8
+
+
+@pytest.mark.gpu
+def test_gpu_large_hole_contours_need_no_label_map():
+    """A ring with a hole above the area threshold, an island in the hole and a hole in the island: outer and
+    hole contours all come from the tables (the reference reports the big hole as an object of its own)."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    lab = np.zeros((2, 513, 513), np.uint8)
+    lab[0, 20:270, 30:480] = 15
+    lab[0, 60:230, 90:420] = 3              # hole: 170 x 330 = 56 100 px
+    lab[0, 100:190, 150:330] = 7            # island in the hole (90 x 180 = 16 200 px)
+    lab[0, 120:160, 180:300] = 0            # hole in the island
+    lab[0, 62, 95:100] = 15                 # specks in the big hole
+    lab[1, 5:280, 5:508] = 7
+    lab[1, 40:240, 40:200] = 12
+    lab[1, 40:240, 201:470] = 9             # two holes separated by a one-pixel wall
+    masks = np.zeros_like(lab)
+    for b in range(2):
+        masks[b, :288] = sp.foreground_mask(lab[b, :288])
+    t = gpu_tables(ssb200, masks, lab, 288, 513, 256)
+
+    def no_label_map():
+        raise AssertionError("label map requested")
+    n_obj = 0
+    for b in range(2):
+        enclosed = ssb200.fold_region_histograms(t["count"][b], t["first"][b], t["parent"][b], t["flags"][b], t["hist"][b],
+                                                 t["ring"][b])
+        got = ssb200.objects_from_regions(masks[b, :288], enclosed, 0.05 * 513 * 513, NAMES, label_map=no_label_map)
+        want = ssb200.objects_from_contours(masks[b, :288], lab[b, :288], 0.05 * 513 * 513, NAMES)
+        assert same_objects(got, want), b
+        n_obj += len(got)
+    assert n_obj >= 5
 
 
 @pytest.mark.gpu
@@ -184,7 +234,8 @@ def test_gpu_regions_full_size_noise_and_overflow():
         masks[b, :288] = sp.foreground_mask(labs[b, :288])
     t = gpu_tables(ssb200, masks, labs, 288, 513, 256)
     for b in range(3):
-        enclosed = ssb200.fold_region_histograms(t["count"][b], t["first"][b], t["parent"][b], t["flags"][b], t["hist"][b])
+        enclosed = ssb200.fold_region_histograms(t["count"][b], t["first"][b], t["parent"][b], t["flags"][b], t["hist"][b],
+                                                 t["ring"][b])
         got = ssb200.objects_from_regions(masks[b, :288], enclosed, 0.05 * 513 * 513, NAMES, label_map=labs[b, :288])
         assert same_objects(got, ssb200.objects_from_contours(masks[b, :288], labs[b, :288], 0.05 * 513 * 513, NAMES))
         assert int(t["hist"][b, :t["count"][b]].sum()) == 288 * 513

@@ -68,7 +68,7 @@ def main():
         ssb200.objects_from_regions(masks_h[i], None, min_area, names, label_map=labs_h[i])
     t0 = time.perf_counter()
     new = [ssb200.objects_from_regions(masks_h[i], ssb200.fold_region_histograms(th["count"][i], th["first"][i], th["parent"][i],
-                                                                                  th["flags"][i], th["hist"][i]),
+                                                                                  th["flags"][i], th["hist"][i], th["ring"][i]),
                                        min_area, names, label_map=labs_h[i]) for i in range(b)]
     t_new = time.perf_counter() - t0
     t0 = time.perf_counter()
