@@ -97,6 +97,39 @@ def test_emulated_ranks_equal_single_pass():
 
 
 @pytest.mark.gpu
+def test_frames_sharded_over_the_visible_gpus_equal_one_gpu():
+    """N-GPU output byte-identical to 1-GPU output.  Uses every visible device (one host
+    thread per GPU, as one process per GPU would); skipped on a single-GPU box."""
+    import threading
+    import torch
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs at least two CUDA devices")
+    import ssb200
+    world, n = torch.cuda.device_count(), 41
+    q = np.random.default_rng(12).integers(0, 256, (n, 513, 513, 21), dtype=np.uint8)
+    labels1, stats1 = ssb200.argmax_stats(torch.from_numpy(q).cuda(0), 288, 513)
+    parts, errors = [None] * world, []
+
+    def run(rank):
+        try:
+            with torch.cuda.device(rank):
+                sched = ssb200.FrameScheduler(rank=rank, world=world, device=rank)
+                s, e = sched.local_range(n)
+                local = torch.from_numpy(q[s:e]).cuda(rank)
+                lab, st = sched.argmax_stats_local(local, 288, 513)
+                torch.cuda.synchronize(rank)
+                parts[rank] = (lab.cpu(), st.cpu())
+        except Exception as exc:
+            errors.append(exc)
+    threads = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors[0]
+    assert torch.equal(torch.cat([p[0] for p in parts]), labels1.cpu())
+    assert torch.equal(torch.cat([p[1] for p in parts]), stats1.cpu())
+
+
+@pytest.mark.gpu
 def test_chunked_streams_equal_single_launch():
     import torch
     if not torch.cuda.is_available():
