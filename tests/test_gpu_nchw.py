@@ -168,6 +168,23 @@ def test_full_batch_agrees_with_interleaved_kernel_and_invariants(ssb):
     assert (stats[:2].cpu().numpy().view(np.uint64) == want_stats).all()
 
 
+def test_hypothesis_shapes(ssb):
+    """Random batch / frame size / ROI / class count / dtype / value range (ties when the range is narrow):
+    frames smaller than a tile (several frames per CTA), odd and even H*W (shifted-pair modes), the
+    generic kernel for other class counts."""
+    from hypothesis import given, settings, strategies as st_
+
+    @settings(max_examples=60, deadline=None)
+    @given(b=st_.integers(1, 5), h=st_.integers(1, 90), w=st_.integers(1, 150), c=st_.sampled_from([2, 19, 21, 21, 33]),
+           half=st_.booleans(), seed=st_.integers(0, 2 ** 31), narrow=st_.booleans(), data=st_.data())
+    def prop(b, h, w, c, half, seed, narrow, data):
+        roi_h = data.draw(st_.integers(1, h)); roi_w = data.draw(st_.integers(1, w))
+        rng = np.random.default_rng(seed)
+        x = rng.integers(-2, 3, (b, c, h, w)).astype(np.float32) if narrow else rng.standard_normal((b, c, h, w)).astype(np.float32)
+        check(ssb, x.astype(np.float16) if half else x, roi_h, roi_w)
+    prop()
+
+
 def test_argument_errors(ssb):
     x = torch.zeros((1, 21, 8, 8), device="cuda")
     with pytest.raises(ssb._cabi.SsbError):
