@@ -122,22 +122,16 @@ def _open_camera(camera_idx):
     return cv2.VideoCapture(camera_idx)
 
 
-def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_area_ratio,
-                          batch_frames=16, mode="contours", device=0, max_frames=None):
-    """Recognize and segment objects from camera frames (sem_seg_server.py:135-213), `batch_frames`
-    frames per GPU pass.  `mode`: "contours" reproduces the reference's objects (per contour of the
-    thresholded colour image); "labels" emits the per-label objects of the fused statistics."""
-    segmented_objects.clear()
-    _, height, width, _ = engine.get_input_tensor_shape()
-    segment_centroid_min_area = min_area_ratio * height * width
-    dev = torch.device("cuda", device)
-    cap = _open_camera(camera_idx)
-    geom = None
-    done = 0
-    staging = hotpath.HostStaging()
-    pinned_frames = None
+def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, mode, dev, out_q, stop):
+    """Feeder thread of recognize_and_segment: reads frames, gathers them into one of two pinned buffers,
+    and enqueues transfer + K1 + model + K2/K3 (+ K4/K5) on its own CUDA stream.  Each batch goes to the
+    consumer as (n_frames, geometry, device results, CUDA event); None ends the stream, an exception is
+    passed through."""
     try:
-        while cap.isOpened():
+        stream = torch.cuda.Stream(dev)
+        pinned, busy = [None, None], [None, None]      # two frame buffers and the event of their last transfer
+        geom, k = None, 0
+        while cap.isOpened() and not stop.is_set():
             frames = []
             while len(frames) < batch_frames:
                 ret, frame = cap.read()
@@ -149,27 +143,80 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
             cam_h, cam_w = frames[0].shape[:2]
             if geom is None or (geom.cam_w, geom.cam_h) != (cam_w, cam_h):
                 geom = hotpath.FrameGeometry(cam_w, cam_h, width, height, keep_aspect_ratio)
-            # frames are gathered straight into a pinned buffer (one host copy, then a DMA transfer); every
-            # batch ends with a synchronising read-back, so the buffer is free again by the next one
-            if pinned_frames is None or pinned_frames.shape[1:] != (cam_h, cam_w, 3):
-                pinned_frames = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8).pin_memory()
-            for i, f in enumerate(frames):
-                pinned_frames[i].copy_(torch.from_numpy(np.ascontiguousarray(f)))
-            batch = pinned_frames[:len(frames)].to(dev, non_blocking=True)
-            inputs = hotpath.preprocess_frames(batch, geom)                       # :150-161
-            logits, scale, zero_point = engine.run_logits(inputs)                 # :162 (model, upstream)
-            nchw = getattr(engine, "layout", "nhwc") == "nchw"
-            if nchw:                                                              # :163-170, :102-122
-                label_maps, stats = hotpath.argmax_stats_nchw(logits, geom.roi_h, geom.roi_w)
-            else:
-                label_maps, stats = hotpath.argmax_stats(logits, geom.roi_h, geom.roi_w)
+            slot = k % 2
+            if busy[slot] is not None:
+                busy[slot].synchronize()               # the transfer that last read this buffer has finished
+            if pinned[slot] is None or pinned[slot].shape[1:] != (cam_h, cam_w, 3):
+                pinned[slot] = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8).pin_memory()
+            for i, f in enumerate(frames):             # one host copy per frame, then a DMA transfer
+                pinned[slot][i].copy_(torch.from_numpy(np.ascontiguousarray(f)))
+            with torch.cuda.stream(stream):
+                batch = pinned[slot][:len(frames)].to(dev, non_blocking=True)
+                busy[slot] = torch.cuda.Event()
+                busy[slot].record(stream)
+                inputs = hotpath.preprocess_frames(batch, geom)                   # :150-161
+                logits, scale, zero_point = engine.run_logits(inputs)             # :162 (model, upstream)
+                nchw = getattr(engine, "layout", "nhwc") == "nchw"
+                if nchw:                                                          # :163-170, :102-122
+                    label_maps, stats = hotpath.argmax_stats_nchw(logits, geom.roi_h, geom.roi_w)
+                else:
+                    label_maps, stats = hotpath.argmax_stats(logits, geom.roi_h, geom.roi_w)
+                res = {"label_maps": label_maps, "stats": stats, "scale": scale, "zero_point": zero_point,
+                       "float_scores": logits.dtype != torch.uint8}
+                if mode == "contours":
+                    masks = hotpath.foreground_mask(label_maps, geom.roi_h, geom.roi_w)   # :173, :79-85
+                    # :98-111 for every contour at once: region tables instead of one polygon fill per contour
+                    res["tables"] = dict(hotpath.blob_regions(masks, label_maps, geom.roi_h, geom.roi_w,
+                                                              logits.shape[1 if nchw else 3], REGION_ROWS), mask=masks)
+                done = torch.cuda.Event()
+                done.record(stream)
+            out_q.put((len(frames), geom, res, done))
+            k += 1
+        out_q.put(None)
+    except BaseException as exc:   # handed to the consumer, which re-raises it
+        out_q.put(exc)
+
+
+def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_area_ratio,
+                          batch_frames=16, mode="contours", device=0, max_frames=None):
+    """Recognize and segment objects from camera frames (sem_seg_server.py:135-213), `batch_frames`
+    frames per GPU pass.  `mode`: "contours" reproduces the reference's objects (per contour of the
+    thresholded colour image); "labels" emits the per-label objects of the fused statistics.
+
+    Two stages run side by side: a feeder thread gathers batch n+1 and enqueues its GPU work while this
+    thread reads back batch n, runs the OpenCV tails and pushes the objects -- in frame order, so the deque
+    looks exactly as the reference's."""
+    import queue
+    import threading
+    segmented_objects.clear()
+    _, height, width, _ = engine.get_input_tensor_shape()
+    segment_centroid_min_area = min_area_ratio * height * width
+    dev = torch.device("cuda", device)
+    cap = _open_camera(camera_idx)
+    done = 0
+    staging = hotpath.HostStaging()
+    batches, stop = queue.Queue(maxsize=1), threading.Event()
+    feeder = threading.Thread(target=_feed_batches, daemon=True,
+                              args=(cap, engine, keep_aspect_ratio, width, height, batch_frames, mode, dev, batches, stop))
+    feeder.start()
+    copy_stream = torch.cuda.Stream(dev)
+    try:
+        while True:
+            item = batches.get()
+            if item is None:
+                break
+            if isinstance(item, BaseException):
+                raise item
+            n_frames, geom, res, ready = item
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(ready)
+                if mode == "contours":
+                    tables_h = staging.fetch(res["tables"])                       # pinned buffers, one wait
+                else:
+                    stats_h = staging.fetch({"stats": res["stats"]})["stats"]
             if mode == "contours":
-                masks = hotpath.foreground_mask(label_maps, geom.roi_h, geom.roi_w)   # :173, :79-85
-                # :98-111 for every contour at once: region tables instead of one polygon fill per contour
-                tables = hotpath.blob_regions(masks, label_maps, geom.roi_h, geom.roi_w, logits.shape[1 if nchw else 3],
-                                              REGION_ROWS)
-                tables_h = staging.fetch(dict(tables, mask=masks))            # pinned buffers, one wait
                 masks_h = tables_h["mask"][:, :geom.roi_h, :geom.roi_w]
+                label_maps = res["label_maps"]
 
                 def contour_tail(i):
                     enclosed = hotpath.fold_region_histograms(tables_h["count"][i], tables_h["first"][i], tables_h["parent"][i],
@@ -180,23 +227,29 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
                         label_map=lambda: label_maps[i, :geom.roi_h, :geom.roi_w].cpu().numpy())
                 # OpenCV releases the GIL: the per-frame contour tails of a batch run side by side;
                 # results are consumed in frame order, so the deque looks exactly as in the reference
-                per_frame = list(_contour_pool().map(contour_tail, range(len(frames))))
+                per_frame = list(_contour_pool().map(contour_tail, range(n_frames)))
             else:
-                stats_h = staging.fetch({"stats": stats})["stats"]
-                shift = 0 if logits.dtype == torch.uint8 else hotpath._cabi.F16_FIXED_SHIFT
-                per_frame = [hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, scale,
-                                                        zero_point, fixed_shift=shift)[0] for i in range(len(frames))]
+                shift = hotpath._cabi.F16_FIXED_SHIFT if res["float_scores"] else 0
+                per_frame = [hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, res["scale"],
+                                                        res["zero_point"], fixed_shift=shift)[0] for i in range(n_frames)]
             for objs in per_frame:
                 for o in objs:
                     lab, score, area, cx, cy = hotpath.normalise(o, width, height)  # :184-192
                     segmented_objects.appendleft(proto.SegmentedObject(
                         label=lab, score=score, area=area, centroid=proto.SegmentedObject.Centroid(cx=cx, cy=cy)))
-            done += len(frames)
+            done += n_frames
             if max_frames is not None and done >= max_frames:
                 break
     except KeyboardInterrupt:
         pass
     finally:
+        stop.set()
+        while feeder.is_alive():                       # unblock a feeder waiting to hand over a batch
+            try:
+                batches.get(timeout=0.05)
+            except queue.Empty:
+                pass
+        feeder.join()
         cap.release()
     return
 
