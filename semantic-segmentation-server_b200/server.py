@@ -148,8 +148,10 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
                 busy[slot].synchronize()               # the transfer that last read this buffer has finished
             if pinned[slot] is None or pinned[slot].shape[1:] != (cam_h, cam_w, 3):
                 pinned[slot] = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8).pin_memory()
-            for i, f in enumerate(frames):             # one host copy per frame, then a DMA transfer
-                pinned[slot][i].copy_(torch.from_numpy(np.ascontiguousarray(f)))
+            # one host copy per frame (spread over the pool: the copies release the GIL), then a DMA transfer
+            dst = pinned[slot]
+            list(_contour_pool().map(lambda i: dst[i].copy_(torch.from_numpy(np.ascontiguousarray(frames[i]))),
+                                     range(len(frames))))
             with torch.cuda.stream(stream):
                 batch = pinned[slot][:len(frames)].to(dev, non_blocking=True)
                 busy[slot] = torch.cuda.Event()
