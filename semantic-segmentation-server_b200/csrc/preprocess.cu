@@ -2,7 +2,7 @@
 // fused into one gather (replaces sem_seg_server.py:150-161: cv2.cvtColor, Image.fromarray,
 // edgetpu resampling_with_original_ratio(NEAREST) = Image.resize + ImageOps.expand, np.asarray().flatten()).
 //
-// One WARP per (frame, output row), four independent warps per CTA, no block-wide barriers:
+// One WARP per (frame, output row), two independent warps per CTA, no block-wide barriers:
 //   1. the sampled source row (Wc*3 bytes, 5760 B at 1080p) is copied into the warp's shared memory
 //      with 16-byte cp.async transfers -- every 32-byte sector of a sampled row is touched by the
 //      11.2-byte sample stride anyway, so reading the row densely costs no extra DRAM traffic and
@@ -23,7 +23,10 @@
 namespace ssb {
 namespace {
 
-constexpr int kPreWarps = 4, kPreThreads = kPreWarps * 32;
+#ifndef SSB_PRE_WARPS
+#define SSB_PRE_WARPS 2   // warps per CTA: 1 -> 35.0 us, 2 -> 29.0, 4 -> 29.8, 8 -> 32.5 (64 frames of 1080p)
+#endif
+constexpr int kPreWarps = SSB_PRE_WARPS, kPreThreads = kPreWarps * 32;
 constexpr int kPrePrefetch = 5;   // quads per lane whose table entries are prefetched: 5 * 32 * 4 >= 513 columns
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
