@@ -102,7 +102,6 @@ __device__ __forceinline__ PixelId pixel_of(const BlobParams &p, int k) {
 }
 
 __global__ void __launch_bounds__(kBlobThreads) blob_init_kernel(const BlobParams p) {
-    pdl_trigger();
     pdl_wait();
     for (int k = 0; k < kBlobRowsPerWarp; ++k) {
     const PixelId q = pixel_of(p, k);
@@ -120,7 +119,6 @@ __global__ void __launch_bounds__(kBlobThreads) blob_init_kernel(const BlobParam
 }
 
 __global__ void __launch_bounds__(kBlobThreads) blob_merge_kernel(const BlobParams p) {
-    pdl_trigger();
     pdl_wait();
     for (int k = 0; k < kBlobRowsPerWarp; ++k) {
     const PixelId q = pixel_of(p, k);
@@ -150,7 +148,6 @@ __global__ void __launch_bounds__(kBlobThreads) blob_merge_kernel(const BlobPara
 }
 
 __global__ void __launch_bounds__(kBlobThreads) blob_flatten_kernel(const BlobParams p) {
-    pdl_trigger();
     pdl_wait();
     for (int k = 0; k < kBlobRowsPerWarp; ++k) {
     const PixelId q = pixel_of(p, k);
@@ -176,7 +173,6 @@ __global__ void __launch_bounds__(kBlobThreads) blob_flatten_kernel(const BlobPa
 // After the flatten pass every par[r] is a root or one step from it (a thread may have read an ancestor
 // before ITS par[] was rewritten), so one more hop settles it.
 __global__ void __launch_bounds__(kBlobThreads) blob_tables_kernel(const BlobParams p) {
-    pdl_trigger();
     pdl_wait();
     for (int k = 0; k < kBlobRowsPerWarp; ++k) {   // warp-uniform: the shuffles below see all 32 lanes
     const PixelId q = pixel_of(p, k);

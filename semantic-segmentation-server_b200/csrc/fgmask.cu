@@ -52,7 +52,6 @@ fg_mask_kernel(const uint8_t *__restrict__ labels, int H, int W, int roi_h, int 
     // luma weight x rounded mean, by channel sum / 64; 512-byte aligned so that a table address is
     // base | offset (one LOP3) instead of base + offset
     __shared__ __align__(512) uint32_t lum[3][32];
-    pdl_trigger();
     pdl_wait();
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         const uint32_t c0 = colormap[3 * i], c1 = colormap[3 * i + 1], c2 = colormap[3 * i + 2];

@@ -39,7 +39,6 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
                           const int *__restrict__ xtab, const int *__restrict__ ytab, int new_w, int new_h,
                           uint8_t *__restrict__ out, int H, int W, int rows_total, int src_bytes, int dst_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
-    pdl_trigger();
     pdl_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row = blockIdx.x * kPreWarps + warp;          // flat (frame, output row)

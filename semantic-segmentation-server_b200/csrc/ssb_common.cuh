@@ -54,11 +54,14 @@ int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out);
 int workspace_release(const WorkspaceLease &lease, cudaStream_t stream);
 
 // ---- programmatic dependent launch ---------------------------------------------------------------
-// Every kernel of the library (1) lets the NEXT kernel in the stream start placing CTAs while its own
-// CTAs retire (`pdl_trigger` at the top) and (2) waits for the kernels it depends on before touching
-// global memory (`pdl_wait`).  Launched through launch_pdl the wait sits behind whatever needs no
-// global memory (barrier init, shared-memory clears), which hides the ~1.5 us between two dependent
-// launches; semantics are those of ordinary stream order.
+// Every kernel of the library waits for the kernels it depends on (`pdl_wait`) only after the part of its
+// prologue that needs no global memory, which hides the ~1.5 us between two dependent launches;
+// semantics are those of ordinary stream order.  Only the SINGLE-WAVE kernels (the argmax kernels: one
+// persistent CTA set that fills the GPU) also call `pdl_trigger` at their top, so that the next kernel's
+// CTAs are placed as theirs retire.  Kernels with many waves of small CTAs (pre-process, mask, regions)
+// must not: a dependent grid becomes schedulable while most of their CTAs have not started yet, and its
+// CTAs then sit in `pdl_wait` on SM resources the remaining waves need (measured: 256-frame pre-process
+// followed by the argmax kernel, 410 us with the early trigger against 330 us without).
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
