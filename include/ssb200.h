@@ -11,8 +11,15 @@
  *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
  *   - the caller owns every input/output buffer and `stats` needs no initialisation.  The only device
  *     memory the library owns is a small zero-at-rest scratch pool per device (a few hundred KB,
- *     cudaMalloc'ed on first use or when a larger batch than ever before arrives) and the
- *     ssb_pipeline objects the caller creates explicitly;
+ *     cudaMalloc'ed on first use or when a larger batch than ever before arrives; that call clears the
+ *     new block on `stream` and waits for the clear) and the ssb_pipeline objects the caller creates
+ *     explicitly.  The argmax kernels leave the scratch zeroed; a block whose kernel could not be
+ *     launched is cleared again before its next use.  A kernel that dies while running (a sticky CUDA
+ *     error: illegal address, ECC, reset) takes the whole CUDA context with it, so there is nothing to
+ *     recover in that case;
+ *   - any number of host threads may call at the same time (each on its own stream for overlap); a
+ *     scratch block belongs to one call from before its launch until the launch is enqueued, and with
+ *     more than 8 calls in that window on one device the ninth waits for one of them;
  *   - CUDA graphs: every device-pointer entry point except ssb_argmax_stats_u8_noalloc may be called
  *     while `stream` is being captured, after the same call (same or larger batch) has run once
  *     outside capture.  A recorded argmax call keeps a scratch block of its own for the life of the
@@ -146,6 +153,11 @@ SSB_API int ssb_argmax_stats_nchw_f16(const uint16_t *logits, int B, int H, int 
 #define SSB_NOALLOC_MAX_FRAMES 256
 SSB_API int ssb_argmax_stats_u8_noalloc(const uint8_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
                                         uint8_t *labels, uint64_t *stats, void *stream);
+/* No counterpart in the reference either: device address and size of that fixed array on the current
+ * device, for a host that wants to look at it or clear it itself (and for the test that fills it with
+ * garbage to show that ssb_argmax_stats_u8_noalloc does not depend on its contents).  Allocates and
+ * launches nothing; the first call on a device does the same address look-up as above. */
+SSB_API int ssb_noalloc_scratch_info(void **device_ptr, size_t *bytes);
 
 /* Replaces sem_seg_server.py:173 (label_to_color_image) + :79-85 (blur 3x3, BGR2GRAY, threshold
  * 127) -- the foreground mask handed to cv2.findContours -- with the exact integer formula.
@@ -188,12 +200,15 @@ SSB_API int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, int 
 /* Host-buffer convenience for callers that hold frames/logits in host memory (the reference's
  * situation: cap.read() and engine.run_inference both return host arrays).
  *
- * An ssb_pipeline owns pinned staging buffers, device buffers and CUDA streams for up to
- * `max_frames_per_chunk` frames per chunk on the current device, created once and reused; the
+ * An ssb_pipeline owns device buffers and CUDA streams (no host memory) for up to
+ * `max_frames_per_chunk` frames per chunk and slot on the current device, created once and reused; the
  * _host call splits the batch into chunks, overlaps host->device copies with the kernels and
- * device->host copies of the results, and returns when `stats_host` (and `labels_host`) are
- * complete.  Host pointers may be pageable; pinned memory (cudaHostAlloc / torch pin_memory) is
- * copied at full PCIe speed. */
+ * device->host copies of the results, and returns when `stats_host` (and `labels_host`) are complete
+ * -- also on failure: it never returns while a copy into or out of the caller's buffers is in flight.
+ * Pass PINNED host memory (cudaHostAlloc / cudaHostRegister / torch pin_memory): it is copied by DMA at
+ * link speed and the chunks overlap.  Pageable pointers are accepted and give the same results, but the
+ * driver then stages every copy through its own bounce buffer and cudaMemcpyAsync blocks the calling
+ * thread until the staging is done, so the overlap between chunks is lost (several times slower). */
 typedef struct ssb_pipeline ssb_pipeline;
 
 SSB_API int ssb_pipeline_create(ssb_pipeline **out, int H, int W, int C, int elem_bytes /*1=u8, 2=f16*/,

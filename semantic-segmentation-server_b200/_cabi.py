@@ -24,6 +24,7 @@ SIGNATURES = {
                                      _c_void_p, _c_void_p, _c_void_p]),
     "ssb_argmax_stats_u8_noalloc": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
                                              _c_void_p, _c_void_p, _c_void_p]),
+    "ssb_noalloc_scratch_info": (_c_int, [ctypes.POINTER(_c_void_p), ctypes.POINTER(ctypes.c_size_t)]),
     "ssb_argmax_stats_f16": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
                                       _c_void_p, _c_void_p, _c_void_p]),
     "ssb_argmax_stats_nchw_f32": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,

@@ -526,7 +526,7 @@ int argmax_stats_planar(const void *logits, int B, int H, int W, int C, int roi_
     p.frame_px = reinterpret_cast<unsigned int *>(static_cast<char *>(ws.ptr) + sizeof(uint64_t) * 4 * C * static_cast<size_t>(B));
     p.divw = make_fastdiv(static_cast<uint32_t>(W));
     const int rc = C == 21 ? dispatch_planar<P, 21>(p, st, nw) : dispatch_planar<P, 19>(p, st, nw);
-    const int rc2 = workspace_release(ws, st);
+    const int rc2 = workspace_release(ws, st, rc == SSB_OK);
     return rc ? rc : rc2;
 }
 

@@ -193,6 +193,6 @@ extern "C" int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W,
     if (int rc = workspace_acquire(scratch_bytes(B, C), st, &ws)) return rc;
     const ArgmaxParams p = make_params(logits, B, H, W, C, roi_h, roi_w, labels, stats64, ws.ptr);
     const int rc = C == 21 ? dispatch_cfg<21>(p, st, nw, stg) : dispatch_cfg<19>(p, st, nw, stg);
-    const int rc2 = workspace_release(ws, st);
+    const int rc2 = workspace_release(ws, st, rc == SSB_OK);
     return rc ? rc : rc2;
 }

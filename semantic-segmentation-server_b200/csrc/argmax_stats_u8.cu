@@ -188,7 +188,7 @@ extern "C" int ssb_argmax_stats_u8(const uint8_t *logits, int B, int H, int W, i
     if (int rc = workspace_acquire(scratch_bytes(B, C), st, &ws)) return rc;
     const ArgmaxParams p = make_params(logits, B, H, W, C, roi_h, roi_w, labels, stats64, ws.ptr);
     const int rc = C == 21 ? dispatch_cfg<21>(p, st, nw, stg) : dispatch_cfg<19>(p, st, nw, stg);
-    const int rc2 = workspace_release(ws, st);
+    const int rc2 = workspace_release(ws, st, rc == SSB_OK);
     return rc ? rc : rc2;
 }
 
@@ -253,4 +253,14 @@ extern "C" int ssb_argmax_stats_u8_noalloc(const uint8_t *logits, int B, int H, 
     SSB_CUDA_TRY(cudaMemsetAsync(scratch, 0, scratch_bytes(B, C), st));
     const ArgmaxParams p = make_params(logits, B, H, W, C, roi_h, roi_w, labels, stats64, scratch);
     return C == 21 ? dispatch_cfg<21>(p, st, nw, stg) : dispatch_cfg<19>(p, st, nw, stg);
+}
+
+// Where the fixed array lives on the current device and how large it is (no allocation, no launch).
+extern "C" int ssb_noalloc_scratch_info(void **device_ptr, size_t *bytes) {
+    using namespace ssb;
+    unsigned char *scratch = nullptr;
+    if (int rc = noalloc_scratch_address(&scratch)) return rc;
+    if (device_ptr) *device_ptr = scratch;
+    if (bytes) *bytes = kNoAllocBytes;
+    return SSB_OK;
 }

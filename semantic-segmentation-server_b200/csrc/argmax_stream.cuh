@@ -215,9 +215,11 @@ __global__ void __launch_bounds__((NWARPS + 1) * 32) argmax_stats_stream_kernel(
                     blk[wi * C * 4 + e] = 0ull;
                 }
                 if (v) atomicAdd(&p.acc[f * (C * 4) + e], v);
-                __threadfence();
             }
         }
+        // every consumer thread: its adds to scratch (these, and those of the scalar stream tail) are
+        // ordered device-wide before the pixel count that may let another CTA collect the frame
+        __threadfence();
         named_bar_sync(1, K::kConsumers);
         if (tid == 0) {
             const unsigned int before = atomicAdd(&p.frame_px[f], static_cast<unsigned int>(covered));

@@ -12,6 +12,7 @@ struct ssb_pipeline {
     int cam_h, cam_w;            // > 0: ingest pipeline (camera frames -> model input), else logits pipeline
     size_t frame_in_bytes, frame_px;
     int32_t *d_xtab, *d_ytab;    // ingest only: device copies of the index tables of the last call
+    cudaEvent_t tables;          // ingest only: "tables are on the device", recorded on slot 0's stream per call
     struct Slot {
         cudaStream_t stream;
         void *d_logits;          // logits chunk, or camera frames chunk (ingest)
@@ -38,6 +39,7 @@ extern "C" int ssb_pipeline_destroy(ssb_pipeline *p) {
     }
     cudaFree(p->d_xtab);
     cudaFree(p->d_ytab);
+    if (p->tables) cudaEventDestroy(p->tables);
     delete p;
     cudaSetDevice(prev);
     return SSB_OK;
@@ -85,30 +87,40 @@ extern "C" int ssb_pipeline_argmax_stats_host(ssb_pipeline *p, const void *logit
     SSB_CUDA_TRY(cudaGetDevice(&dev));
     if (dev != p->device) return fail(SSB_ERR_BAD_SHAPE, "pipeline belongs to device %d, current is %d", p->device, dev);
     const size_t stats_frame = sizeof(uint64_t) * 4 * p->C;
-    int chunk = 0;
-    for (int b0 = 0; b0 < B; b0 += p->max_frames, ++chunk) {
+    int rc = SSB_OK, chunk = 0;
+    auto cuda_ok = [&](cudaError_t e, const char *what) {
+        if (e != cudaSuccess) rc = fail(SSB_ERR_CUDA, "%s failed: %s", what, cudaGetErrorString(e));
+        return e == cudaSuccess;
+    };
+    for (int b0 = 0; b0 < B && rc == SSB_OK; b0 += p->max_frames, ++chunk) {
         const int nb = B - b0 < p->max_frames ? B - b0 : p->max_frames;
         auto &s = p->slots[chunk % p->n_slots];
         // stream order makes the slot's buffers safe to reuse: the previous chunk's D2H copies are
         // ahead of this H2D copy on the same stream
         const char *src = static_cast<const char *>(logits_host) + p->frame_in_bytes * b0;
-        SSB_CUDA_TRY(cudaMemcpyAsync(s.d_logits, src, p->frame_in_bytes * nb, cudaMemcpyHostToDevice, s.stream));
-        int rc;
+        if (!cuda_ok(cudaMemcpyAsync(s.d_logits, src, p->frame_in_bytes * nb, cudaMemcpyHostToDevice, s.stream), "H2D copy"))
+            break;
         if (p->elem_bytes == 1)
             rc = ssb_argmax_stats_u8(static_cast<const uint8_t *>(s.d_logits), nb, p->H, p->W, p->C, roi_h, roi_w,
                                      labels_host ? s.d_labels : nullptr, s.d_stats, s.stream);
         else
             rc = ssb_argmax_stats_f16(static_cast<const uint16_t *>(s.d_logits), nb, p->H, p->W, p->C, roi_h, roi_w,
                                       labels_host ? s.d_labels : nullptr, s.d_stats, s.stream);
-        if (rc) return rc;
-        SSB_CUDA_TRY(cudaMemcpyAsync(reinterpret_cast<char *>(stats_host) + stats_frame * b0, s.d_stats,
-                                     stats_frame * nb, cudaMemcpyDeviceToHost, s.stream));
+        if (rc) break;
+        if (!cuda_ok(cudaMemcpyAsync(reinterpret_cast<char *>(stats_host) + stats_frame * b0, s.d_stats, stats_frame * nb,
+                                     cudaMemcpyDeviceToHost, s.stream), "D2H copy of the statistics"))
+            break;
         if (labels_host)
-            SSB_CUDA_TRY(cudaMemcpyAsync(labels_host + p->frame_px * b0, s.d_labels, p->frame_px * nb,
-                                         cudaMemcpyDeviceToHost, s.stream));
+            cuda_ok(cudaMemcpyAsync(labels_host + p->frame_px * b0, s.d_labels, p->frame_px * nb, cudaMemcpyDeviceToHost,
+                                    s.stream), "D2H copy of the label maps");
     }
-    for (int i = 0; i < p->n_slots; ++i) SSB_CUDA_TRY(cudaStreamSynchronize(p->slots[i].stream));
-    return SSB_OK;
+    // Also on failure: copies of earlier chunks into the caller's buffers may still be in flight, and the
+    // caller is free to release those buffers as soon as this returns.
+    for (int i = 0; i < p->n_slots; ++i) {
+        const cudaError_t e = cudaStreamSynchronize(p->slots[i].stream);
+        if (e != cudaSuccess && rc == SSB_OK) rc = fail(SSB_ERR_CUDA, "stream sync failed: %s", cudaGetErrorString(e));
+    }
+    return rc;
 }
 
 // ---- ingest: camera frames held on the host -> model inputs (row f3 of SURVEY.md section 8) ----------
@@ -129,6 +141,7 @@ extern "C" int ssb_pipeline_create_ingest(ssb_pipeline **out, int Hc, int Wc, in
     cudaError_t e = cudaGetDevice(&p->device);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_xtab, sizeof(int32_t) * W);
     if (e == cudaSuccess) e = cudaMalloc(&p->d_ytab, sizeof(int32_t) * H);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->tables, cudaEventDisableTiming);
     for (int i = 0; e == cudaSuccess && p->slots && i < n_slots; ++i) {
         auto &s = p->slots[i];
         e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
@@ -156,15 +169,19 @@ extern "C" int ssb_pipeline_preprocess_host(ssb_pipeline *p, const uint8_t *fram
     int dev = 0;
     SSB_CUDA_TRY(cudaGetDevice(&dev));
     if (dev != p->device) return fail(SSB_ERR_BAD_SHAPE, "pipeline belongs to device %d, current is %d", p->device, dev);
-    // tables first, on slot 0's stream; the other slots wait for them through an event
-    cudaStream_t s0 = p->slots[0].stream;
-    SSB_CUDA_TRY(cudaMemcpyAsync(p->d_xtab, xtab_host, sizeof(int32_t) * new_w, cudaMemcpyHostToDevice, s0));
-    SSB_CUDA_TRY(cudaMemcpyAsync(p->d_ytab, ytab_host, sizeof(int32_t) * new_h, cudaMemcpyHostToDevice, s0));
-    cudaEvent_t tables;
-    SSB_CUDA_TRY(cudaEventCreateWithFlags(&tables, cudaEventDisableTiming));
-    SSB_CUDA_TRY(cudaEventRecord(tables, s0));
-    for (int i = 1; i < p->n_slots; ++i) SSB_CUDA_TRY(cudaStreamWaitEvent(p->slots[i].stream, tables, 0));
+    // tables first, on slot 0's stream; the other slots wait for them through an event.  Nothing below
+    // returns before the final synchronisation of every slot.
     int rc = SSB_OK, chunk = 0;
+    auto cuda_ok = [&](cudaError_t e, const char *what) {
+        if (e != cudaSuccess && rc == SSB_OK) rc = fail(SSB_ERR_CUDA, "%s failed: %s", what, cudaGetErrorString(e));
+        return e == cudaSuccess;
+    };
+    cudaStream_t s0 = p->slots[0].stream;
+    cuda_ok(cudaMemcpyAsync(p->d_xtab, xtab_host, sizeof(int32_t) * new_w, cudaMemcpyHostToDevice, s0), "table copy") &&
+        cuda_ok(cudaMemcpyAsync(p->d_ytab, ytab_host, sizeof(int32_t) * new_h, cudaMemcpyHostToDevice, s0), "table copy") &&
+        cuda_ok(cudaEventRecord(p->tables, s0), "cudaEventRecord");
+    for (int i = 1; i < p->n_slots && rc == SSB_OK; ++i)
+        cuda_ok(cudaStreamWaitEvent(p->slots[i].stream, p->tables, 0), "cudaStreamWaitEvent");
     for (int b0 = 0; b0 < B && rc == SSB_OK; b0 += p->max_frames, ++chunk) {
         const int nb = B - b0 < p->max_frames ? B - b0 : p->max_frames;
         auto &s = p->slots[chunk % p->n_slots];
@@ -182,6 +199,5 @@ extern "C" int ssb_pipeline_preprocess_host(ssb_pipeline *p, const uint8_t *fram
         const cudaError_t e = cudaStreamSynchronize(p->slots[i].stream);
         if (e != cudaSuccess && rc == SSB_OK) rc = fail(SSB_ERR_CUDA, "stream sync failed: %s", cudaGetErrorString(e));
     }
-    cudaEventDestroy(tables);
     return rc;
 }

@@ -41,9 +41,11 @@ int device_info(DeviceInfo *out);
 
 // ---- scratch workspaces ------------------------------------------------------------------------
 // Device scratch that is ZERO AT REST (kernels leave it zeroed).  A small per-device pool, grown on
-// demand with cudaMalloc (first use, or a larger request than seen before).  A slot that was last
-// used on another stream is ordered behind that use with an event, so concurrent streams never share
-// live scratch.  A call made while its stream is being captured into a CUDA graph gets a block of its
+// demand with cudaMalloc (first use, or a larger request than seen before).  A slot belongs to one
+// caller between acquire and release (other callers take another slot, or wait when all are out), and a
+// slot that was last used on another stream is ordered behind that use with an event, so concurrent
+// streams never share live scratch.  `launch_ok = false` on release (the kernel could not be launched)
+// marks the block for re-zeroing before its next use.  A call made while its stream is being captured into a CUDA graph gets a block of its
 // own that no other call ever uses (slot == -1 in the lease); those blocks are sized by earlier eager
 // calls, so the same call must have run once outside capture.
 struct WorkspaceLease {
@@ -51,7 +53,7 @@ struct WorkspaceLease {
     int dev, slot;
 };
 int workspace_acquire(size_t bytes, cudaStream_t stream, WorkspaceLease *out);
-int workspace_release(const WorkspaceLease &lease, cudaStream_t stream);
+int workspace_release(const WorkspaceLease &lease, cudaStream_t stream, bool launch_ok = true);
 
 // ---- programmatic dependent launch ---------------------------------------------------------------
 // Every kernel of the library waits for the kernels it depends on (`pdl_wait`) only after the part of its

@@ -68,3 +68,46 @@ def test_threads_on_their_own_streams(ssb):
         th.join()
     torch.cuda.synchronize()
     assert not errors, errors[0]
+
+
+def test_more_threads_than_scratch_slots(ssb):
+    """The scratch pool has 8 slots per device.  Twelve threads on twelve streams keep more calls than
+    that between 'slot taken' and 'kernel enqueued': a slot must never be handed to two of them (the
+    ninth caller waits for a slot to come back), so every result stays the lone call's."""
+    rng = np.random.default_rng(99)
+    n_threads, rounds = 12, 40
+    work = []
+    for t in range(n_threads):
+        q = rng.integers(0, 256, (1 + t % 3, 120, 131, 21), dtype=np.uint8)
+        work.append((q, cport.argmax_stats(q, 100, 131, threads=2)))
+    errors = []
+    start = threading.Barrier(n_threads)
+
+    def run(t):
+        try:
+            q_np, want = work[t]
+            stream = torch.cuda.Stream()
+            with torch.cuda.stream(stream):
+                q = torch.from_numpy(q_np).cuda()
+                stream.synchronize()
+                start.wait()
+                for r in range(rounds):
+                    lab, st = ssb.argmax_stats(q, 100, 131, stream=stream)
+                    if r % 8 == 7:
+                        stream.synchronize()
+                        if not ((lab.cpu().numpy() == want[0]).all() and (st.cpu().numpy().view(np.uint64) == want[1]).all()):
+                            raise AssertionError("thread %d round %d: result differs from the oracle" % (t, r))
+        except Exception as e:
+            errors.append(e)
+            try:
+                start.abort()
+            except Exception:
+                pass
+
+    threads = [threading.Thread(target=run, args=(t,)) for t in range(n_threads)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    torch.cuda.synchronize()
+    assert not errors, errors[0]
