@@ -32,14 +32,21 @@ def _p(a):
     return a.ctypes.data_as(ctypes.c_void_p)
 
 
-def argmax_stats(logits, roi_h=None, roi_w=None, threads=1, want_labels=True):
-    """logits [B,H,W,C] u8 or f16 (C-contiguous) -> (labels [B,H,W] u8 | None, stats [B,C,4] u64)."""
+def argmax_stats(logits, roi_h=None, roi_w=None, threads=1, want_labels=True, out=None):
+    """logits [B,H,W,C] u8 or f16 (C-contiguous) -> (labels [B,H,W] u8 | None, stats [B,C,4] u64).
+    `out=(labels, stats)` reuses the caller's arrays (a timed loop should not fault fresh pages in)."""
     logits = np.ascontiguousarray(logits)
     b, h, w, c = logits.shape
     roi_h = h if roi_h is None else roi_h
     roi_w = w if roi_w is None else roi_w
-    labels = np.empty((b, h, w), np.uint8) if want_labels else None
-    stats = np.zeros((b, c, 4), np.uint64)
+    if out is not None:
+        labels, stats = out
+        assert stats.shape == (b, c, 4) and stats.dtype == np.uint64 and stats.flags.c_contiguous
+        assert labels is None or (labels.shape == (b, h, w) and labels.dtype == np.uint8 and labels.flags.c_contiguous)
+        want_labels = labels is not None
+    else:
+        labels = np.empty((b, h, w), np.uint8) if want_labels else None
+        stats = np.zeros((b, c, 4), np.uint64)
     fn = {np.dtype(np.uint8): "oracle_argmax_stats_u8",
           np.dtype(np.float16): "oracle_argmax_stats_f16"}[logits.dtype]
     rc = getattr(lib(), fn)(_p(logits), b, h, w, c, roi_h, roi_w,

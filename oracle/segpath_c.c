@@ -131,48 +131,99 @@ static void frame_fg_mask(const uint8_t *lab, int h, int w, int ld, const uint8_
         }
 }
 
-/* ---- frame-sharded thread pool (frames are independent: sem_seg_server.py:145-195) ---- */
+/* ---- frame-sharded thread pool (frames are independent: sem_seg_server.py:145-195) ----
+ * Workers are created once and kept (a timed CPU baseline should not pay pthread_create per batch);
+ * frames are handed out one at a time from a shared counter, the calling thread works too. */
 typedef struct {
     int kind;            /* 0 u8 argmax, 1 f16 argmax, 2 preprocess */
     const void *in; void *out; uint64_t *stats;
-    int b0, b1, H, W, C, roi_h, roi_w;
+    int B, H, W, C, roi_h, roi_w;
     int Hc, Wc, new_w, new_h; const int32_t *xtab, *ytab; int64_t in_stride;
 } job_t;
 
-static void *worker(void *arg) {
-    job_t *j = (job_t *)arg;
+static void do_frame(const job_t *j, int b) {
     size_t px = (size_t)j->H * j->W;
-    for (int b = j->b0; b < j->b1; ++b) {
-        if (j->kind == 0)
-            frame_argmax_stats_u8((const uint8_t *)j->in + (size_t)b * px * j->C, j->H, j->W, j->C, j->roi_h,
-                                  j->roi_w, j->out ? (uint8_t *)j->out + (size_t)b * px : NULL,
-                                  j->stats + (size_t)b * j->C * 4);
-        else if (j->kind == 1)
-            frame_argmax_stats_f16((const uint16_t *)j->in + (size_t)b * px * j->C, j->H, j->W, j->C, j->roi_h,
-                                   j->roi_w, j->out ? (uint8_t *)j->out + (size_t)b * px : NULL,
-                                   j->stats + (size_t)b * j->C * 4);
-        else
-            frame_preprocess((const uint8_t *)j->in + (size_t)b * j->in_stride, j->Wc, j->xtab, j->ytab,
-                             j->new_w, j->new_h, (uint8_t *)j->out + (size_t)b * px * 3, j->H, j->W);
+    if (j->kind == 0)
+        frame_argmax_stats_u8((const uint8_t *)j->in + (size_t)b * px * j->C, j->H, j->W, j->C, j->roi_h,
+                              j->roi_w, j->out ? (uint8_t *)j->out + (size_t)b * px : NULL,
+                              j->stats + (size_t)b * j->C * 4);
+    else if (j->kind == 1)
+        frame_argmax_stats_f16((const uint16_t *)j->in + (size_t)b * px * j->C, j->H, j->W, j->C, j->roi_h,
+                               j->roi_w, j->out ? (uint8_t *)j->out + (size_t)b * px : NULL,
+                               j->stats + (size_t)b * j->C * 4);
+    else
+        frame_preprocess((const uint8_t *)j->in + (size_t)b * j->in_stride, j->Wc, j->xtab, j->ytab,
+                         j->new_w, j->new_h, (uint8_t *)j->out + (size_t)b * px * 3, j->H, j->W);
+}
+
+#define POOL_MAX 512
+static struct {
+    pthread_mutex_t mu;
+    pthread_cond_t work, done;
+    pthread_t tid[POOL_MAX];
+    int n_workers;          /* threads created so far */
+    int helpers;            /* workers invited to the current job: ids < helpers */
+    unsigned generation;    /* bumped per job */
+    int running;            /* invited workers that have not finished the current job yet */
+    const job_t *job;
+    int next_frame;         /* next frame to hand out (atomic) */
+} g_pool = {PTHREAD_MUTEX_INITIALIZER, PTHREAD_COND_INITIALIZER, PTHREAD_COND_INITIALIZER, {0}, 0, 0, 0, 0, NULL, 0};
+static pthread_mutex_t g_call_mu = PTHREAD_MUTEX_INITIALIZER;   /* one sharded call at a time */
+
+static void drain(const job_t *j) {
+    for (;;) {
+        int b = __atomic_fetch_add(&g_pool.next_frame, 1, __ATOMIC_RELAXED);
+        if (b >= j->B) return;
+        do_frame(j, b);
+    }
+}
+
+static void *pool_worker(void *arg) {
+    const int id = (int)(intptr_t)arg;
+    unsigned seen = 0;
+    pthread_mutex_lock(&g_pool.mu);
+    for (;;) {
+        while (g_pool.generation == seen || id >= g_pool.helpers) {
+            if (g_pool.generation != seen) seen = g_pool.generation;   /* not invited to this one */
+            pthread_cond_wait(&g_pool.work, &g_pool.mu);
+        }
+        seen = g_pool.generation;
+        const job_t *j = g_pool.job;
+        pthread_mutex_unlock(&g_pool.mu);
+        drain(j);
+        pthread_mutex_lock(&g_pool.mu);
+        if (--g_pool.running == 0) pthread_cond_signal(&g_pool.done);
     }
     return NULL;
 }
 
-static int run_sharded(job_t *proto, int B, int threads) {
-    if (threads < 1) threads = 1;
-    if (threads > B) threads = B > 0 ? B : 1;
-    pthread_t *tid = (pthread_t *)malloc(sizeof(pthread_t) * threads);
-    job_t *jobs = (job_t *)malloc(sizeof(job_t) * threads);
-    if (!tid || !jobs) { free(tid); free(jobs); return -1; }
-    for (int t = 0; t < threads; ++t) {
-        jobs[t] = *proto;
-        jobs[t].b0 = (int)((int64_t)B * t / threads);
-        jobs[t].b1 = (int)((int64_t)B * (t + 1) / threads);
-        if (t == threads - 1) worker(&jobs[t]);
-        else pthread_create(&tid[t], NULL, worker, &jobs[t]);
+static int run_sharded(job_t *j, int B, int threads) {
+    j->B = B;
+    if (threads > B) threads = B;
+    if (threads > POOL_MAX + 1) threads = POOL_MAX + 1;
+    if (threads <= 1) {
+        for (int b = 0; b < B; ++b) do_frame(j, b);
+        return 0;
     }
-    for (int t = 0; t < threads - 1; ++t) pthread_join(tid[t], NULL);
-    free(tid); free(jobs);
+    pthread_mutex_lock(&g_call_mu);
+    pthread_mutex_lock(&g_pool.mu);
+    while (g_pool.n_workers < threads - 1) {
+        if (pthread_create(&g_pool.tid[g_pool.n_workers], NULL, pool_worker, (void *)(intptr_t)g_pool.n_workers)) break;
+        pthread_detach(g_pool.tid[g_pool.n_workers]);
+        ++g_pool.n_workers;
+    }
+    g_pool.helpers = threads - 1 < g_pool.n_workers ? threads - 1 : g_pool.n_workers;
+    g_pool.running = g_pool.helpers;
+    g_pool.job = j;
+    __atomic_store_n(&g_pool.next_frame, 0, __ATOMIC_RELAXED);
+    ++g_pool.generation;
+    pthread_cond_broadcast(&g_pool.work);
+    pthread_mutex_unlock(&g_pool.mu);
+    drain(j);
+    pthread_mutex_lock(&g_pool.mu);
+    while (g_pool.running > 0) pthread_cond_wait(&g_pool.done, &g_pool.mu);
+    pthread_mutex_unlock(&g_pool.mu);
+    pthread_mutex_unlock(&g_call_mu);
     return 0;
 }
 
