@@ -321,8 +321,9 @@ def other_kernels(ssb200, torch):
     # instead of filling one polygon per contour
     mask_b = torch.empty_like(lab_b)
     us_m = _time_us(torch, lambda i: ssb200.foreground_mask(lab_b, CAM_ROI_H, CAM_ROI_W, cm, out=mask_b), 20)
-    us_r = _time_us(torch, lambda i: ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024), 20)
-    regions = ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024)["count"].float().mean().item()
+    tabs = ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024)
+    us_r = _time_us(torch, lambda i: ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024, out=tabs), 20)
+    regions = tabs["count"].float().mean().item()
     out.append({"kernel": "fg_mask + blob_regions, blobby label maps, ROI 288x513 (batch 64)", "us_fg_mask": us_m,
                 "us_blob_regions": us_r, "frames_per_s": b / (us_m + us_r) * 1e6, "regions_per_frame": regions})
     del qb, field, lab_true

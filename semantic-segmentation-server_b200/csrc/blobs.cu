@@ -14,9 +14,22 @@
 // the enclosing region that are 4-adjacent to the hole: it encloses the hole, what is nested in it, and
 // that ring, whose label histogram is the `ring` row of the hole.
 //
-// Labelling: union-find over the ROI with atomicMin links (larger root under smaller, so a region's root
-// IS its first pixel): init, merge (west / north-west / north / north-east for foreground, west / north
-// for background), flatten, then slot assignment for roots and warp-aggregated histogram atomics.
+// Labelling: union-find with atomicMin links (larger root under smaller, so a region's root IS its first
+// pixel): run-based initial links, merge (west / north-west / north / north-east for foreground, west /
+// north for background), flatten, then table rows for roots and warp-aggregated histogram atomics.
+//
+// Two implementations with the same tables:
+//   * blob_cluster_kernel (ROIs whose eighth fits 16-bit pixel indices: everything up to ~720x720): ONE
+//     launch, one thread-block cluster of 8 CTAs per frame, a CTA per horizontal strip.  The mask lives in
+//     shared memory as bit rows (all neighbour tests are word operations, uniform over the warp that owns
+//     a 32-pixel segment), the union-find of a strip in shared memory with 16-bit ids.  Global memory only
+//     sees what crosses strips: one parent word and one row number per LOCAL ROOT (sparse use of the two
+//     scratch planes), the ids of each strip's first and last row, and the tables.  Phases are separated
+//     by cluster barriers.  DRAM traffic: mask and label map once.
+//   * blob_{init,merge,flatten,tables}_kernel: the whole union-find in global memory, any ROI size.
+#include <cstring>
+#include <mutex>
+
 #include "ssb_common.cuh"
 
 namespace ssb {
@@ -226,12 +239,16 @@ __global__ void __launch_bounds__(kBlobThreads) blob_tables_kernel(const BlobPar
     }
 }
 
+
+#include "blobs_cluster.cuh"   // blob_cluster_kernel: one thread-block cluster per frame
+
 }  // namespace
 }  // namespace ssb
 
 extern "C" size_t ssb_blob_regions_scratch_bytes(int B, int roi_h, int roi_w) {
     if (B < 0 || roi_h < 0 || roi_w < 0) return 0;
-    return sizeof(int) * 2 * static_cast<size_t>(B) * roi_h * roi_w;
+    // two int32 planes (union-find parents, table rows) + the ids of the first / last row of every strip
+    return sizeof(int) * static_cast<size_t>(B) * (2 * static_cast<size_t>(roi_h) * roi_w + ssb::kStrips * 2 * static_cast<size_t>(roi_w));
 }
 
 extern "C" int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, int B, int H, int W, int roi_h, int roi_w,
@@ -256,11 +273,70 @@ extern "C" int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, i
     p.root = static_cast<int *>(scratch);
     p.slot = p.root + n;
     p.count = count; p.first = first; p.parent = parent; p.flags = flags; p.hist = hist; p.ring = ring;
+    if (B > 65535) return fail(SSB_ERR_LIMIT, "B must be <= 65535");
+    // one cluster per frame when a strip (an eighth of the ROI's rows) fits 16-bit pixel indices and shared memory
+    {
+        StripParams sp{};
+        sp.b = p;
+        sp.rows = (roi_h + kStrips - 1) / kStrips;
+        sp.S = (roi_w + 31) / 32;
+        sp.divS = make_fastdiv(static_cast<uint32_t>(sp.S > 1 ? sp.S : 2));
+        sp.divW = make_fastdiv(static_cast<uint32_t>(roi_w > 1 ? roi_w : 2));
+        sp.edge = p.slot + n;
+        sp.L = strip_layout(sp.rows, sp.S, roi_w, C);
+        const size_t smem = static_cast<size_t>(sp.L.total);
+        DeviceInfo di;
+        if (int rc = device_info(&di)) return rc;
+        const char *force = getenv("SSB_BLOB_PATH");   // tuning / test knob: "global" = the global-memory kernels
+        const bool want_global = force && !strcmp(force, "global");
+        if (!want_global && static_cast<long long>(sp.rows) * roi_w <= 65535 && max_regions <= 0xFFFF &&
+            smem <= static_cast<size_t>(di.max_smem_optin)) {
+            static std::mutex mu;
+            static size_t smem_set[64] = {0};
+            int dev = 0;
+            SSB_CUDA_TRY(cudaGetDevice(&dev));
+            if (dev < 0 || dev >= 64) return fail(SSB_ERR_LIMIT, "device ordinal %d not supported", dev);
+            {
+                std::lock_guard<std::mutex> lock(mu);
+                if (smem_set[dev] < smem) {
+                    SSB_CUDA_TRY(cudaFuncSetAttribute(blob_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                      static_cast<int>(smem)));
+                    // all of the SM's L1 / shared-memory array as shared memory: with the default split only three
+                    // CTAs fit an SM and 48 clusters the GPU -- a batch of 64 frames then runs as two waves
+                    SSB_CUDA_TRY(cudaFuncSetAttribute(blob_cluster_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                                      cudaSharedmemCarveoutMaxShared));
+                    smem_set[dev] = smem;
+                }
+            }
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(kStrips, B);
+            cfg.blockDim = dim3(kStripThreads);
+            cfg.dynamicSmemBytes = smem;
+            cfg.stream = st;
+            cudaLaunchAttribute attr[2];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = kStrips;
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[1].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 2;
+            if (getenv("SSB_BLOB_DEBUG")) {   // tuning aid: how many clusters the GPU holds at once
+                int n_clusters = 0;
+                cudaOccupancyMaxActiveClusters(&n_clusters, blob_cluster_kernel, &cfg);
+                fprintf(stderr, "blob_cluster_kernel: %d threads, %zu B shared memory, %d clusters of %d active at once\n",
+                        kStripThreads, smem, n_clusters, kStrips);
+            }
+            SSB_CUDA_TRY(cudaLaunchKernelEx(&cfg, blob_cluster_kernel, sp));
+            return SSB_OK;
+        }
+    }
     SSB_CUDA_TRY(cudaMemsetAsync(count, 0, sizeof(int) * B, st));
     SSB_CUDA_TRY(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * static_cast<size_t>(B) * max_regions * C, st));
     if (ring) SSB_CUDA_TRY(cudaMemsetAsync(ring, 0, sizeof(uint32_t) * static_cast<size_t>(B) * max_regions * C, st));
     constexpr int kRowsPerCta = 8 * kBlobRowsPerWarp;
-    if (B > 65535 || (roi_h + kRowsPerCta - 1) / kRowsPerCta > 65535) return fail(SSB_ERR_LIMIT, "B and roi_h/64 must be <= 65535");
+    if ((roi_h + kRowsPerCta - 1) / kRowsPerCta > 65535) return fail(SSB_ERR_LIMIT, "roi_h/64 must be <= 65535");
     const dim3 grid((roi_w + 31) / 32, (roi_h + kRowsPerCta - 1) / kRowsPerCta, B), block(32, 8);
     SSB_CUDA_TRY(launch_pdl(blob_init_kernel, grid, block, 0, st, p));
     SSB_CUDA_TRY(launch_pdl(blob_merge_kernel, grid, block, 0, st, p));

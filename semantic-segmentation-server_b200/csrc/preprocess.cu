@@ -18,6 +18,8 @@
 // are built on the host (Pillow accumulates `xo += scale` in double; see the host module's
 // nearest_index_table).  An earlier version used one CTA per row with byte-wise staging and was
 // issue-bound (65 % issue slots at 30 % DRAM utilisation).
+#include <cstring>
+
 #include "ssb_common.cuh"
 
 namespace ssb {
@@ -34,6 +36,7 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src)
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+template <bool kStore32>
 __global__ void __launch_bounds__(kPreThreads)
 preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_stride, int Wc,
                           const int *__restrict__ xtab, const int *__restrict__ ytab, int new_w, int new_h,
@@ -96,8 +99,13 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             if (xs[j] >= 0) {
-                const uint8_t *p = sp + xs[j] * 3;
-                px[j] = static_cast<uint32_t>(p[2]) | (static_cast<uint32_t>(p[1]) << 8) | (static_cast<uint32_t>(p[0]) << 16);
+                // the pixel's 3 bytes sit in one or two aligned words: two 32-bit loads, a funnel shift and a
+                // byte permute (three byte loads per pixel took half again as many shared-memory wavefronts
+                // at the 11.2-byte sample stride)
+                const uint32_t o = sphase + static_cast<uint32_t>(xs[j]) * 3u;
+                const uint32_t *wp = reinterpret_cast<const uint32_t *>(src) + (o >> 2);
+                const uint32_t bgr = __funnelshift_r(wp[0], wp[1], (o & 3u) * 8u);
+                px[j] = __byte_perm(bgr, 0u, 0x4012);
             } else {
                 px[j] = 0u;   // right of the resized image: ImageOps.expand padding
             }
@@ -116,8 +124,21 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
     }
     __syncwarp();
 
-    // 3. staging row -> global: byte head, 128-bit body re-aligned by (ohead mod 4) bytes, byte tail
     const uint8_t *dbytes = reinterpret_cast<const uint8_t *>(dst);
+    if (kStore32) {
+        // 3. staging row -> global as 32-bit words: lane l moves word l of every group of 32, so both the
+        //    shared-memory reads (two per word, for the re-alignment by 0-3 bytes) and the global stores
+        //    (128 contiguous bytes per instruction) are conflict-free; byte stores for the ragged ends
+        const int h4 = min(out_bytes, static_cast<int>((4 - (reinterpret_cast<uintptr_t>(grow) & 3)) & 3));
+        for (int i = lane; i < h4; i += 32) grow[i] = dbytes[i];
+        const int nwords = (out_bytes - h4) >> 2;
+        const int sh = h4 * 8;
+        uint32_t *gw = reinterpret_cast<uint32_t *>(grow + h4);
+        for (int i = lane; i < nwords; i += 32) gw[i] = __funnelshift_r(dst[i], dst[i + 1], sh);
+        for (int i = h4 + nwords * 4 + lane; i < out_bytes; i += 32) grow[i] = dbytes[i];
+        return;
+    }
+    // 3. staging row -> global: byte head, 128-bit body re-aligned by (ohead mod 4) bytes, byte tail
     for (int i = lane; i < ohead; i += 32) grow[i] = dbytes[i];
     const int wsh = (ohead & 3) * 8;          // bit offset of the body inside the staging words
     const uint32_t *dw = dst + (ohead >> 2);  // first staging word that holds body bytes
@@ -158,10 +179,12 @@ extern "C" int ssb_preprocess_nearest_u8(const uint8_t *frames_bgr, int B, int H
     DeviceInfo di;
     if (int rc = device_info(&di)) return rc;
     if (smem > di.max_smem_optin) return fail(SSB_ERR_LIMIT, "row of %d px needs %d B shared memory", Wc, smem);
-    if (smem > 48 * 1024)
-        SSB_CUDA_TRY(cudaFuncSetAttribute(preprocess_nearest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const char *env = getenv("SSB_PRE_STORE");   // tuning knob: "128" = 128-bit stores from 4-way conflicting reads
+    const bool store32 = !(env && !strcmp(env, "128"));
+    auto kern = store32 ? preprocess_nearest_kernel<true> : preprocess_nearest_kernel<false>;
+    if (smem > 48 * 1024) SSB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const unsigned grid = static_cast<unsigned>((rows_total + kPreWarps - 1) / kPreWarps);
-    SSB_CUDA_TRY(launch_pdl(preprocess_nearest_kernel, dim3(grid), dim3(kPreThreads), smem,
+    SSB_CUDA_TRY(launch_pdl(kern, dim3(grid), dim3(kPreThreads), smem,
                             static_cast<cudaStream_t>(stream), frames_bgr, static_cast<long long>(frame_stride), Wc, xtab,
                             ytab, new_w, new_h, out_rgb, H, W, static_cast<int>(rows_total), src_bytes, dst_bytes));
     return SSB_OK;

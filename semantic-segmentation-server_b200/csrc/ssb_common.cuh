@@ -142,6 +142,14 @@ __device__ __forceinline__ void bulk_copy_g2s(void *dst_smem, const void *src_gm
         : "memory");
 }
 
+// The same copy without a cache hint (data that other kernels read again).
+__device__ __forceinline__ void bulk_copy_g2s_plain(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                     "r"(smem_addr(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

@@ -287,24 +287,37 @@ class HostStaging:
         return {k: v.numpy() for k, v in out.items()}
 
 
-def blob_regions(masks, label_maps, roi_h, roi_w, num_classes=21, max_regions=256, stream=None):
+class RegionTables(dict):
+    """The tensors blob_regions returns; `.scratch` is the device block the kernels worked in (kept so that
+    `out=` can reuse it)."""
+    scratch = None
+
+
+def blob_regions(masks, label_maps, roi_h, roi_w, num_classes=21, max_regions=256, stream=None, out=None):
     """[B,H,W] u8 masks + label maps (device) -> region tables of every frame's ROI, as a dict of device
     tensors: count [B], first / parent / flags [B,R] int32, hist and ring [B,R,num_classes] int32 (C-ABI:
-    ssb_blob_regions_u8).  Copy them to the host and hand one frame's rows to fold_region_histograms."""
+    ssb_blob_regions_u8; rows at or beyond count[b] are not written).  Copy them to the host and hand one
+    frame's rows to fold_region_histograms.  `out`: the dict an earlier call with the same shapes returned,
+    to reuse its tensors (and the scratch block it carries) instead of allocating."""
     _require_cuda(masks, "masks")
     _require_cuda(label_maps, "label_maps")
     b, h, w = masks.shape
     dev = masks.device
-    scratch = torch.empty(_cabi.lib.ssb_blob_regions_scratch_bytes(b, roi_h, roi_w), dtype=torch.uint8, device=dev)
-    t = {"count": torch.empty((b,), dtype=torch.int32, device=dev),
-         "first": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
-         "parent": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
-         "flags": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
-         "hist": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev),
-         "ring": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev)}
+    n_scratch = _cabi.lib.ssb_blob_regions_scratch_bytes(b, roi_h, roi_w)
+    t = out
+    if (t is None or t["count"].shape[0] != b or t["first"].shape[1] != max_regions or t["hist"].shape[2] != num_classes
+            or t.scratch.numel() < n_scratch or t["count"].device != dev):
+        t = RegionTables(
+            {"count": torch.empty((b,), dtype=torch.int32, device=dev),
+             "first": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
+             "parent": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
+             "flags": torch.empty((b, max_regions), dtype=torch.int32, device=dev),
+             "hist": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev),
+             "ring": torch.empty((b, max_regions, num_classes), dtype=torch.int32, device=dev)})
+        t.scratch = torch.empty(n_scratch, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         _cabi.check(_cabi.lib.ssb_blob_regions_u8(
-            masks.data_ptr(), label_maps.data_ptr(), b, h, w, roi_h, roi_w, num_classes, max_regions, scratch.data_ptr(),
+            masks.data_ptr(), label_maps.data_ptr(), b, h, w, roi_h, roi_w, num_classes, max_regions, t.scratch.data_ptr(),
             t["count"].data_ptr(), t["first"].data_ptr(), t["parent"].data_ptr(), t["flags"].data_ptr(),
             t["hist"].data_ptr(), t["ring"].data_ptr(), _stream_ptr(stream)))
     return t

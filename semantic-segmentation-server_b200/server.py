@@ -131,6 +131,7 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
         stream = torch.cuda.Stream(dev)
         pinned, busy = [None, None], [None, None]      # two frame buffers and the event of their last transfer
         geom, k = None, 0
+        tables = [None] * 4
         while cap.isOpened() and not stop.is_set():
             frames = []
             while len(frames) < batch_frames:
@@ -168,8 +169,10 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
                 if mode == "contours":
                     masks = hotpath.foreground_mask(label_maps, geom.roi_h, geom.roi_w)   # :173, :79-85
                     # :98-111 for every contour at once: region tables instead of one polygon fill per contour
-                    res["tables"] = dict(hotpath.blob_regions(masks, label_maps, geom.roi_h, geom.roi_w,
-                                                              logits.shape[1 if nchw else 3], REGION_ROWS), mask=masks)
+                    # the table tensors rotate over four sets: one being filled, one queued, one being read back
+                    tables[k % 4] = hotpath.blob_regions(masks, label_maps, geom.roi_h, geom.roi_w,
+                                                         logits.shape[1 if nchw else 3], REGION_ROWS, out=tables[k % 4])
+                    res["tables"] = dict(tables[k % 4], mask=masks)
                 done = torch.cuda.Event()
                 done.record(stream)
             out_q.put((len(frames), geom, res, done))

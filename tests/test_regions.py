@@ -125,11 +125,15 @@ def gpu_tables(ssb, masks, labs, roi_h, roi_w, max_regions):
 
 
 @pytest.mark.gpu
-def test_gpu_region_tables_match_scipy_labelling():
+@pytest.mark.parametrize("path", ["cluster", "global"])
+def test_gpu_region_tables_match_scipy_labelling(path, monkeypatch):
+    """Both implementations behind ssb_blob_regions_u8: one thread-block cluster per frame with the labelling in
+    shared memory (the default for ROIs of this size), and the global-memory kernels that take any ROI."""
     torch = pytest.importorskip("torch")
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     import ssb200
+    monkeypatch.setenv("SSB_BLOB_PATH", path)
     rng = np.random.default_rng(9)
     H, W = 96, 130
     for roi_h, roi_w in ((96, 130), (57, 130), (96, 77), (40, 33)):
@@ -243,3 +247,34 @@ def test_gpu_regions_full_size_noise_and_overflow():
     assert t["count"][3] == count
     if count > 256:
         assert ssb200.fold_region_histograms(t["count"][3], t["first"][3], t["parent"][3], t["flags"][3], t["hist"][3]) is None
+
+
+@pytest.mark.gpu
+def test_gpu_regions_wide_roi_and_many_rows():
+    """Shapes around the limits of the cluster kernel: an ROI whose strips are wider than one warp-word row
+    count (1 x N, N x 1, 3 x 700), more table rows than fit 16 bits (-> global-memory kernels), a ROI narrower
+    than the frame (no staged copy), and a batch of frames with different contents."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    rng = np.random.default_rng(21)
+    for (H, W, roi_h, roi_w, rows) in ((5, 700, 3, 700, 512), (300, 9, 300, 1, 64), (40, 64, 1, 64, 64),
+                                       (130, 200, 129, 200, 70000), (200, 300, 200, 300, 4096), (64, 96, 64, 95, 300)):
+        labs = rng.choice([0, 7, 15, 3], size=(5, H, W), p=[.45, .2, .25, .1]).astype(np.uint8)
+        labs[0] = 15
+        labs[1] = 0
+        masks = np.zeros_like(labs)
+        for b in range(5):
+            masks[b, :roi_h, :roi_w] = sp.foreground_mask(labs[b, :roi_h, :roi_w])
+        t = gpu_tables(ssb200, masks, labs, roi_h, roi_w, rows)
+        for b in range(5):
+            count, first, parent, flags, hist, ring = scipy_table(masks[b, :roi_h, :roi_w], labs[b, :roi_h, :roi_w])
+            assert t["count"][b] == count, (H, W, b)
+            if count > rows:
+                continue
+            order = np.argsort(t["first"][b, :count])
+            for name, want in (("first", first), ("parent", parent), ("flags", flags), ("hist", hist)):
+                assert (t[name][b, :count][order] == want).all(), (H, W, b, name)
+            holes = (flags & 3) == 0
+            assert (t["ring"][b, :count][order][holes] == ring[holes]).all(), (H, W, b)
