@@ -424,11 +424,11 @@ class FixedScores:
         return self.q[:x.shape[0]], 1.0 / 16, 128
 
 
-def reply_e2e(ssb200, torch, n_frames=1024, batch=32):
+def reply_e2e(ssb200, torch, n_frames=2048, batch=64):
     """Camera frames in pinned host memory -> recognize_and_segment(mode="contours") -> SegmentedObject
     protos in the deque: everything sem_seg_server.py:144-195 does per frame except the model, through
     the drop-in producer loop (H2D of every frame, K1, K2+K3, K4, K5, read-back of masks and region tables,
-    OpenCV contour tail, reply normalisation, protobuf construction)."""
+    OpenCV contour stage on worker processes, reply normalisation, protobuf construction)."""
     import importlib
     srv = importlib.import_module(ssb200.__name__ + ".server")
     g = torch.Generator(); g.manual_seed(3)

@@ -187,6 +187,7 @@ SSB_API int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int roi_h
  *                of `first`; -1 when `first` is in column 0
  *   flags        [B][max_regions] bit 0: foreground region; bit 1: background region touching the ROI
  *                border (not a hole: it is the outside)
+ *   (rows at or beyond count[b] are not written: the tables need no clearing and hold garbage there)
  *   hist         [B][max_regions][C] u32 label histogram of the region's own pixels
  *   ring         [B][max_regions][C] u32 or NULL: for a hole (background region not touching the border), the
  *                label histogram of the enclosing foreground region's pixels that are 4-adjacent to it --
@@ -230,6 +231,32 @@ SSB_API int ssb_pipeline_create_ingest(ssb_pipeline **out, int Hc, int Wc, int H
 SSB_API int ssb_pipeline_preprocess_host(ssb_pipeline *p, const uint8_t *frames_bgr_host, int B,
                                          const int32_t *xtab_host, const int32_t *ytab_host, int new_w, int new_h,
                                          uint8_t *out_rgb_host);
+
+/* Host-side helpers of a producer loop that feeds the entry points above (sem_seg_server.py:144-195 for a
+ * batch of frames).  Both run on host threads the library keeps in a small pool; both take HOST pointers
+ * except `dst_device`.
+ *
+ * ssb_frames_to_device: the frames cap.read() returned (sem_seg_server.py:146; n separate host arrays of
+ * frame_bytes each) -> one device batch [n][frame_bytes] on `stream`.  A frame that already sits in
+ * page-locked memory is sent by DMA from where it is; the others are copied by up to `threads` host threads
+ * into `staging_host` (page-locked, n * frame_bytes, may be NULL if no frame needs it) and sent from there
+ * frame by frame, so gathering and DMA overlap.  Returns when every copy is enqueued: do not reuse
+ * `staging_host` (or the frames) before `stream` has passed this point. */
+SSB_API int ssb_frames_to_device(const uint8_t *const *frames_host, int n, size_t frame_bytes, uint8_t *staging_host,
+                                 uint8_t *dst_device, int threads, void *stream);
+
+/* ssb_fold_regions_host: the region tables of B frames (outputs of ssb_blob_regions_u8 copied to the host, same
+ * shapes) -> what each contour encloses, i.e. what sem_seg_server.py:98-107 counts under a filled polygon.
+ *   enclosed  [B][max_regions][C] i64: for a foreground region, the label histogram of the region, its holes and
+ *             everything nested in them (its OUTER contour); for a hole, that of the hole, everything nested in
+ *             it and its ring (its HOLE contour; without `ring`, NULL, the ring is left out); rows of the outside
+ *             background are not meaningful
+ *   order     [B][max_regions] i32: the first count[b] entries are the table rows sorted by `first`
+ *             (look a contour up by the first pixel of its region with a binary search)
+ *   complete  [B] u8: 0 where count[b] > max_regions (table incomplete: use the per-contour fill for that frame) */
+SSB_API int ssb_fold_regions_host(int B, int C, int max_regions, const int32_t *count, const int32_t *first,
+                                  const int32_t *parent, const int32_t *flags, const uint32_t *hist, const uint32_t *ring,
+                                  int64_t *enclosed, int32_t *order, uint8_t *complete, int threads);
 
 #ifdef __cplusplus
 }

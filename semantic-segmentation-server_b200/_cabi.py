@@ -36,6 +36,9 @@ SIGNATURES = {
     "ssb_blob_regions_scratch_bytes": (ctypes.c_size_t, [_c_int, _c_int, _c_int]),
     "ssb_blob_regions_u8": (_c_int, [_c_void_p, _c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int,
                                      _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p]),
+    "ssb_frames_to_device": (_c_int, [_c_void_p, _c_int, ctypes.c_size_t, _c_void_p, _c_void_p, _c_int, _c_void_p]),
+    "ssb_fold_regions_host": (_c_int, [_c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p,
+                                       _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_int]),
     "ssb_pipeline_create": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),
     "ssb_pipeline_destroy": (_c_int, [_c_void_p]),
     "ssb_pipeline_create_ingest": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),

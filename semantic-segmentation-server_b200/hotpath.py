@@ -356,19 +356,66 @@ def fold_region_histograms(count, first, parent, flags, hist, ring=None):
     return out
 
 
-def hole_first_pixel(contour, mask):
-    """First pixel (raster order, y*w + x) of the hole a hole contour of `mask` goes around.  The contour
-    runs through the foreground pixels 4-adjacent to the hole, so its top row is one above the hole's, and
-    a background pixel directly below a contour pixel of that row can only belong to this hole."""
-    pts = contour[:, 0, :]
-    y_top = int(pts[:, 1].min())
-    nxt = np.roll(pts, -1, axis=0)
-    on = pts[:, 1] == y_top
-    xs = set(int(x) for x in pts[on, 0])
-    for a, b in zip(pts[on & (nxt[:, 1] == y_top), 0], nxt[on & (nxt[:, 1] == y_top), 0]):
-        xs.update(range(int(min(a, b)), int(max(a, b)) + 1))     # CHAIN_APPROX_SIMPLE keeps only a run's end points
-    below = [x for x in sorted(xs) if mask[y_top + 1, x] == 0]
-    return (y_top + 1) * mask.shape[1] + below[0] if below else None
+def fold_regions_batch(tables_host, threads=8, scratch=None):
+    """Region tables of a batch (host numpy arrays: the dict blob_regions returned, copied to the host) ->
+    one EnclosedHistograms (or None: table incomplete) per frame.  Same results as fold_region_histograms
+    frame by frame; the folding runs in the library on `threads` host threads (C-ABI: ssb_fold_regions_host).
+    `scratch`: a dict kept by the caller between calls (work arrays are reused)."""
+    count, first, parent, flags = (np.ascontiguousarray(tables_host[k]) for k in ("count", "first", "parent", "flags"))
+    hist = np.ascontiguousarray(tables_host["hist"])
+    ring = tables_host.get("ring")
+    ring = None if ring is None else np.ascontiguousarray(ring)
+    b, r, c = hist.shape
+    scratch = {} if scratch is None else scratch
+    if scratch.get("shape") != (b, r, c):
+        scratch.update(shape=(b, r, c), enc=np.empty((b, r, c), np.int64), order=np.empty((b, r), np.int32),
+                       complete=np.empty((b,), np.uint8))
+    enc, order, complete = scratch["enc"], scratch["order"], scratch["complete"]
+    _cabi.check(_cabi.lib.ssb_fold_regions_host(
+        b, c, r, count.ctypes.data, first.ctypes.data, parent.ctypes.data, flags.ctypes.data, hist.ctypes.data,
+        None if ring is None else ring.ctypes.data, enc.ctypes.data, order.ctypes.data, complete.ctypes.data, threads))
+    out = []
+    for i in range(b):
+        if not complete[i]:
+            out.append(None)
+            continue
+        rows = order[i, :int(count[i])]
+        keys = first[i][rows].tolist()
+        kind = (flags[i][rows] & 3).tolist()          # 1 / 3: foreground; 0: hole; 2: the outside
+        rows = rows.tolist()
+        enc_i = enc[i]
+        e = EnclosedHistograms((k, enc_i[j].copy()) for k, j, f in zip(keys, rows, kind) if f & 1)
+        e.holes = {k: enc_i[j].copy() for k, j, f in zip(keys, rows, kind) if f == 0} if ring is not None else {}
+        out.append(e)
+    return out
+
+
+def frames_to_device(frames, dst, staging=None, threads=8, stream=None):
+    """The frames cap.read() returned (a list of equally shaped C-contiguous uint8 arrays) -> dst[:len(frames)]
+    (device tensor [B,Hc,Wc,3]) on `stream` (C-ABI: ssb_frames_to_device).  Frames in page-locked memory are
+    sent from where they are, the others through `staging` (pinned tensor of dst's shape).  The copies are
+    asynchronous: keep `frames` and `staging` untouched until the stream has passed this point."""
+    import ctypes
+    n = len(frames)
+    if n == 0:
+        return dst
+    _require_cuda(dst, "dst")
+    shape = tuple(dst.shape[1:])
+    ptrs = (ctypes.c_void_p * n)()
+    for i, f in enumerate(frames):
+        if not (isinstance(f, np.ndarray) and f.dtype == np.uint8 and f.shape == shape and f.flags.c_contiguous):
+            raise ValueError("frame %d is not a C-contiguous uint8 array of shape %s" % (i, shape))
+        ptrs[i] = f.ctypes.data
+    frame_bytes = int(np.prod(shape))
+    if staging is not None and (not staging.is_pinned() or staging.numel() < n * frame_bytes):
+        raise ValueError("staging must be a pinned tensor of at least %d bytes" % (n * frame_bytes))
+    with torch.cuda.device(dst.device):
+        _cabi.check(_cabi.lib.ssb_frames_to_device(ptrs, n, frame_bytes, None if staging is None else staging.data_ptr(),
+                                                   dst.data_ptr(), threads, _stream_ptr(stream)))
+    return dst
+
+
+from .contour_worker import hole_first_pixel  # noqa: E402,F401  (shared with the worker processes; no torch there)
 
 
 def objects_from_regions(mask, enclosed, min_area, labels, label_map=None):

@@ -19,7 +19,7 @@ import os
 import numpy as np
 import torch
 
-from . import hotpath, proto
+from . import contour_pool, hotpath, proto
 
 # Stack (LIFO deque) shared by the producer thread and the RPC handlers (sem_seg_server.py:28).
 segmented_objects = collections.deque()
@@ -104,8 +104,26 @@ class ArrayCamera:
 
 
 REGION_ROWS = 256     # rows of the per-frame region table; frames with more regions use the polygon fill
+HOST_THREADS = min(16, len(os.sched_getaffinity(0)))   # host threads of the native helpers (frame gather, table fold)
 
+CONTOUR_WORKERS = int(os.environ.get("SSB_CONTOUR_WORKERS", min(8, max(1, len(os.sched_getaffinity(0)) // 2))))
 _pool = None
+_workers = None
+
+
+def _contour_workers(n_workers, slot_bytes):
+    """The process-wide contour worker pool (started on first use, restarted when a larger batch arrives)."""
+    global _workers
+    n_workers = CONTOUR_WORKERS if n_workers is None else n_workers
+    if n_workers <= 0:
+        return None
+    if _workers is None or _workers.slot_bytes < slot_bytes or len(_workers._procs) != n_workers:
+        if _workers is not None:
+            _workers.close()
+        _workers = contour_pool.ContourWorkers(n_workers, slot_bytes)
+        import atexit
+        atexit.register(_workers.close)
+    return _workers
 
 
 def _contour_pool():
@@ -130,6 +148,7 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
     try:
         stream = torch.cuda.Stream(dev)
         pinned, busy = [None, None], [None, None]      # two frame buffers and the event of their last transfer
+        device_in, held = [None, None], [None, None]
         geom, k = None, 0
         tables = [None] * 4
         while cap.isOpened() and not stop.is_set():
@@ -146,15 +165,17 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
                 geom = hotpath.FrameGeometry(cam_w, cam_h, width, height, keep_aspect_ratio)
             slot = k % 2
             if busy[slot] is not None:
-                busy[slot].synchronize()               # the transfer that last read this buffer has finished
+                busy[slot].synchronize()               # the transfer that last read this slot's buffers has finished
             if pinned[slot] is None or pinned[slot].shape[1:] != (cam_h, cam_w, 3):
                 pinned[slot] = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8).pin_memory()
-            # one host copy per frame (spread over the pool: the copies release the GIL), then a DMA transfer
-            dst = pinned[slot]
-            list(_contour_pool().map(lambda i: dst[i].copy_(torch.from_numpy(np.ascontiguousarray(frames[i]))),
-                                     range(len(frames))))
+                device_in[slot] = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8, device=dev)
+            frames = [f if (f.dtype == np.uint8 and f.flags.c_contiguous) else np.ascontiguousarray(f, np.uint8) for f in frames]
+            held[slot] = frames                        # frames in page-locked memory are read by the DMA where they are
             with torch.cuda.stream(stream):
-                batch = pinned[slot][:len(frames)].to(dev, non_blocking=True)
+                # native: pageable frames are gathered into the pinned buffer by host threads and sent frame by
+                # frame (gather and DMA overlap), page-locked ones go straight from their own memory
+                batch = hotpath.frames_to_device(frames, device_in[slot], pinned[slot], threads=HOST_THREADS,
+                                                 stream=stream)[:len(frames)]
                 busy[slot] = torch.cuda.Event()
                 busy[slot].record(stream)
                 inputs = hotpath.preprocess_frames(batch, geom)                   # :150-161
@@ -183,14 +204,15 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
 
 
 def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_area_ratio,
-                          batch_frames=16, mode="contours", device=0, max_frames=None):
+                          batch_frames=16, mode="contours", device=0, max_frames=None, contour_workers=None):
     """Recognize and segment objects from camera frames (sem_seg_server.py:135-213), `batch_frames`
     frames per GPU pass.  `mode`: "contours" reproduces the reference's objects (per contour of the
     thresholded colour image); "labels" emits the per-label objects of the fused statistics.
 
     Two stages run side by side: a feeder thread gathers batch n+1 and enqueues its GPU work while this
     thread reads back batch n, runs the OpenCV tails and pushes the objects -- in frame order, so the deque
-    looks exactly as the reference's."""
+    looks exactly as the reference's.  `contour_workers`: processes for the OpenCV contour stage (None: as
+    many as CONTOUR_WORKERS; 0: in this process, on threads)."""
     import queue
     import threading
     segmented_objects.clear()
@@ -198,8 +220,9 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
     segment_centroid_min_area = min_area_ratio * height * width
     dev = torch.device("cuda", device)
     cap = _open_camera(camera_idx)
-    done = 0
+    done = n_batches = 0
     staging = hotpath.HostStaging()
+    fold_scratch = {}
     batches, stop = queue.Queue(maxsize=1), threading.Event()
     feeder = threading.Thread(target=_feed_batches, daemon=True,
                               args=(cap, engine, keep_aspect_ratio, width, height, batch_frames, mode, dev, batches, stop))
@@ -213,26 +236,42 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
             if isinstance(item, BaseException):
                 raise item
             n_frames, geom, res, ready = item
+            workers = _contour_workers(contour_workers, batch_frames * height * width) if mode == "contours" else None
             with torch.cuda.stream(copy_stream):
                 copy_stream.wait_event(ready)
-                if mode == "contours":
+                if mode == "contours" and workers is not None:
+                    # masks go by DMA into the shared-memory slot the worker processes read; tables to pinned buffers
+                    slot = n_batches % workers.n_slots
+                    masks_sh = workers.slot(slot, (n_frames, height, width))
+                    masks_sh.copy_(res["tables"]["mask"][:n_frames], non_blocking=True)
+                    tables_h = staging.fetch({k: v for k, v in res["tables"].items() if k != "mask"})   # one wait for all
+                    tables_h["mask"] = masks_sh.numpy()
+                elif mode == "contours":
                     tables_h = staging.fetch(res["tables"])                       # pinned buffers, one wait
                 else:
                     stats_h = staging.fetch({"stats": res["stats"]})["stats"]
+            n_batches += 1
             if mode == "contours":
                 masks_h = tables_h["mask"][:, :geom.roi_h, :geom.roi_w]
                 label_maps = res["label_maps"]
+                if workers is not None:
+                    workers.submit(slot, n_frames, height, width, geom.roi_h, geom.roi_w, segment_centroid_min_area)
+                # what every contour encloses, for the whole batch at once (native, HOST_THREADS threads)
+                enclosed = hotpath.fold_regions_batch(tables_h, HOST_THREADS, fold_scratch)
 
                 def contour_tail(i):
-                    enclosed = hotpath.fold_region_histograms(tables_h["count"][i], tables_h["first"][i], tables_h["parent"][i],
-                                                              tables_h["flags"][i], tables_h["hist"][i], tables_h["ring"][i])
                     # the label map is only needed for frames with more regions than table rows: fetched on demand
                     return hotpath.objects_from_regions(
-                        masks_h[i], enclosed, segment_centroid_min_area, labels,
+                        masks_h[i], enclosed[i], segment_centroid_min_area, labels,
                         label_map=lambda: label_maps[i, :geom.roi_h, :geom.roi_w].cpu().numpy())
-                # OpenCV releases the GIL: the per-frame contour tails of a batch run side by side;
-                # results are consumed in frame order, so the deque looks exactly as in the reference
-                per_frame = list(_contour_pool().map(contour_tail, range(n_frames)))
+                if workers is not None:
+                    # findContours / contourArea / moments ran in the worker processes (cv2.findContours does not
+                    # run in parallel on threads); here the candidates meet the region tables, in frame order
+                    candidates = workers.collect()
+                    per_frame = [contour_pool.objects_from_candidates(candidates[i], enclosed[i], labels) for i in range(n_frames)]
+                    per_frame = [contour_tail(i) if objs is None else objs for i, objs in enumerate(per_frame)]
+                else:
+                    per_frame = list(_contour_pool().map(contour_tail, range(n_frames)))
             else:
                 shift = hotpath._cabi.F16_FIXED_SHIFT if res["float_scores"] else 0
                 per_frame = [hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, res["scale"],

@@ -1,0 +1,107 @@
+"""The native host-side helpers of the producer loop: batch fold of the region tables (no GPU needed) and the
+frame upload that sends page-locked frames from where they are and gathers the others with host threads."""
+import numpy as np
+import pytest
+
+from test_regions import random_label_map, scipy_table
+
+
+def test_native_fold_equals_the_python_fold():
+    import ssb200
+    rng = np.random.default_rng(4)
+    R, B = 2048, 40
+    count = np.zeros(B, np.int32)
+    first, parent, flags = (np.full((B, R), -7, np.int32) for _ in range(3))      # garbage beyond count, as on the GPU
+    hist, ring = (np.full((B, R, 21), 0x55555555, np.uint32) for _ in range(2))
+    want = []
+    for b in range(B):
+        mask, lab = random_label_map(rng, b)
+        n, f, p, fl, h, rg = scipy_table(mask, lab)
+        perm = rng.permutation(n)                       # the kernel hands out rows with an atomic counter
+        count[b] = n
+        first[b, :n], parent[b, :n], flags[b, :n], hist[b, :n], ring[b, :n] = f[perm], p[perm], fl[perm], h[perm], rg[perm]
+        want.append(ssb200.fold_region_histograms(n, f, p, fl, h, rg))
+    count[3], want[3] = R + 5, None                     # an overflowed table
+    tables = {"count": count, "first": first, "parent": parent, "flags": flags, "hist": hist, "ring": ring}
+    scratch = {}
+    for threads in (1, 5):                              # the second call reuses the work arrays
+        got = ssb200.fold_regions_batch(tables, threads=threads, scratch=scratch)
+        for b in range(B):
+            if want[b] is None:
+                assert got[b] is None
+                continue
+            assert set(got[b]) == set(want[b]) and set(got[b].holes) == set(want[b].holes), b
+            assert all((got[b][k] == want[b][k]).all() for k in want[b]), b
+            assert all((got[b].holes[k] == want[b].holes[k]).all() for k in want[b].holes), b
+    no_ring = ssb200.fold_regions_batch({k: v for k, v in tables.items() if k != "ring"}, threads=2)
+    assert all(g is None or (not g.holes and all((g[k] == w[k]).all() for k in w)) for g, w in zip(no_ring, want))
+
+
+@pytest.mark.gpu
+def test_frames_to_device_mixed_pinned_and_pageable():
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    rng = np.random.default_rng(8)
+    shape = (97, 131, 3)
+    pinned_src = torch.from_numpy(rng.integers(0, 256, (4,) + shape, dtype=np.uint8)).pin_memory().numpy()
+    frames = []
+    for i in range(11):
+        frames.append(pinned_src[i % 4] if i % 3 == 0 else rng.integers(0, 256, shape, dtype=np.uint8))
+    dst = torch.zeros((16,) + shape, dtype=torch.uint8, device="cuda")
+    staging = torch.empty((16,) + shape, dtype=torch.uint8).pin_memory()
+    stream = torch.cuda.Stream()
+    for threads in (1, 6):
+        dst.zero_()
+        torch.cuda.synchronize()
+        ssb200.frames_to_device(frames, dst, staging, threads=threads, stream=stream)
+        stream.synchronize()
+        assert (dst[:11].cpu().numpy() == np.stack(frames)).all()
+        assert int(dst[11:].count_nonzero()) == 0
+    # only page-locked frames: no staging buffer needed; pageable ones without it: refused
+    ssb200.frames_to_device([pinned_src[1], pinned_src[2]], dst, None, stream=stream)
+    stream.synchronize()
+    assert (dst[:2].cpu().numpy() == pinned_src[1:3]).all()
+    with pytest.raises(ssb200._cabi.SsbError):
+        ssb200.frames_to_device([frames[1]], dst, None, stream=stream)
+    with pytest.raises(ValueError):
+        ssb200.frames_to_device([frames[1][:, :50]], dst, staging, stream=stream)
+
+
+def test_contour_worker_processes_give_the_in_process_objects():
+    """The OpenCV contour stage on worker processes (masks in shared memory) + region tables = the objects of
+    the polygon-fill path, in the same order; frames the tables cannot answer for come back as None."""
+    import importlib
+    import ssb200
+    from oracle import segpath as sp
+    from test_regions import NAMES, same_objects
+    cp = importlib.import_module(ssb200.__name__ + ".contour_pool")
+    rng = np.random.default_rng(12)
+    H, W, roi_h, roi_w, n = 120, 160, 100, 160, 10
+    labs = np.zeros((n, H, W), np.uint8)
+    for i in range(n):
+        m, l = random_label_map(rng, i)
+        hh, ww = min(H, l.shape[0]), min(W, l.shape[1])
+        labs[i, :hh, :ww] = l[:hh, :ww]
+    labs[0, 10:90, 20:150] = 15
+    labs[0, 30:70, 50:120] = 3                      # a hole above the area threshold
+    masks = np.zeros_like(labs)
+    for i in range(n):
+        masks[i, :roi_h, :roi_w] = sp.foreground_mask(labs[i, :roi_h, :roi_w])
+    workers = cp.ContourWorkers(3, n * H * W, n_slots=2)
+    try:
+        workers.slot(1, (n, H, W)).numpy()[:] = masks
+        for min_area in (0.0, 40.0):
+            workers.submit(1, n, H, W, roi_h, roi_w, min_area)
+            cands = workers.collect()
+            assert len(cands) == n
+            for i in range(n):
+                enc = ssb200.fold_region_histograms(*scipy_table(masks[i, :roi_h, :roi_w], labs[i, :roi_h, :roi_w]))
+                got = cp.objects_from_candidates(cands[i], enc, NAMES)
+                want = ssb200.objects_from_contours(masks[i, :roi_h, :roi_w], labs[i, :roi_h, :roi_w], min_area, NAMES)
+                assert got is not None and same_objects(got, want), (i, min_area)
+                if cands[i]:
+                    assert cp.objects_from_candidates(cands[i], None, NAMES) is None
+    finally:
+        workers.close()
