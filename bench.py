@@ -664,17 +664,29 @@ def run_ssb(args):
     if not ((out_labels[-1:] == want_l).all() and (out_stats[-1:] == want_s).all()):
         raise SystemExit("bench: e2e result differs from the oracle")
     pipe.close()
-    del pinned
+    # the same bytes as plain page-locked host -> device copies, every rank at once, the same fixed work per rank:
+    # what the host side of this box can deliver to N GPUs pulling together (the ceiling of `e2e`)
+    dst = torch.empty_like(dev_batches[0])
+    dst.copy_(pinned[0], non_blocking=True)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        dst.copy_(pinned[i % 2], non_blocking=True)
+    torch.cuda.synchronize()
+    link_s = time.perf_counter() - t0
+    barrier()
+    del pinned, dst
 
     # ---- max over ranks ------------------------------------------------------------------------------
-    times = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    times = torch.tensor([dev_ms, e2e_s * 1e3, link_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-        per_rank_e2e = [None] * world
+        per_rank_e2e, per_rank_link = [None] * world, [None] * world
         dist.all_gather_object(per_rank_e2e, BATCH * e2e_steps / e2e_s)
+        dist.all_gather_object(per_rank_link, BATCH * e2e_steps * H * W * C / link_s / 1e9)
     else:
-        per_rank_e2e = [BATCH * e2e_steps / e2e_s]
-    dev_ms, e2e_ms = float(times[0]), float(times[1])
+        per_rank_e2e, per_rank_link = [BATCH * e2e_steps / e2e_s], [BATCH * e2e_steps * H * W * C / link_s / 1e9]
+    dev_ms, e2e_ms, link_ms = float(times[0]), float(times[1]), float(times[2])
     barrier()
 
     if rank == 0:
@@ -731,6 +743,11 @@ def run_ssb(args):
                     "d2h_bytes_per_step": world * BATCH * (H * W + C * 32), "steps": e2e_steps,
                     "per_rank_frames_per_s": per_rank_e2e,
                     "per_rank_h2d_GBps": [f * H * W * C / 1e9 for f in per_rank_e2e],
+                    "link_ceiling": {"value": world * BATCH * e2e_steps / (link_ms * 1e-3), "unit": "frames/s",
+                                     "per_rank_GBps": per_rank_link,
+                                     "how": "the same %d x 354 MB per rank as plain page-locked host->device copies, all ranks "
+                                            "at once, max over ranks (no kernels, no read-back)" % e2e_steps},
+                    "frac_of_link_ceiling": (world * BATCH * e2e_steps / (e2e_ms * 1e-3)) / (world * BATCH * e2e_steps / (link_ms * 1e-3)),
                     "api": "ssb_pipeline_argmax_stats_host (pinned host buffers, 3 streams x 16-frame chunks)"},
             "e2e_reply": reply,
             "multi_gpu_identity": identity,

@@ -32,6 +32,10 @@
 
 #include "argmax_stream.cuh"
 
+#ifndef SSB_PLANAR_PREFETCH
+#define SSB_PLANAR_PREFETCH 0   // rejected: 124 -> 171 us for 64 fp16 frames (profiles/experiments/r02_nchw_l2_prefetch.log)
+#endif
+
 namespace ssb {
 namespace {
 
@@ -378,6 +382,28 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
             y_base = fastdiv(static_cast<uint32_t>(r0), p.divw);
             k = 0;
         }
+#if SSB_PLANAR_PREFETCH
+        // The C plane chunks this warp reads in the NEXT tile are requested from DRAM now (one bulk prefetch into
+        // L2 per plane, issued by one lane): a thread holds all its loads of a tile in registers, so it cannot
+        // have two tiles in flight itself, and with four warps per scheduler DRAM latency was not covered.
+        if (lane == 0 && t + 1 < t1) {
+            long long fn = f;
+            int in = i + 1;
+            if (in == p.tiles_per_frame) { in = 0; ++fn; }
+            const int rn = in * kTilePx + kChunk * warp;
+            const int n_px = min(kChunk, p.hw - rn);
+            if (n_px > 0) {
+                const char *q = reinterpret_cast<const char *>(static_cast<const T *>(p.logits) + (fn * C * p.hw + rn));
+                const long long plane_bytes = static_cast<long long>(p.hw) * P::kBytes;
+#pragma unroll
+                for (int c = 0; c < C; ++c, q += plane_bytes) {
+                    const uintptr_t a = reinterpret_cast<uintptr_t>(q) & ~static_cast<uintptr_t>(15);
+                    const uintptr_t e = (reinterpret_cast<uintptr_t>(q) + static_cast<uintptr_t>(n_px) * P::kBytes) & ~static_cast<uintptr_t>(15);
+                    if (e > a) bulk_prefetch_l2(reinterpret_cast<const void *>(a), static_cast<uint32_t>(e - a));
+                }
+            }
+        }
+#endif
         const int n_valid = min(kTilePx, p.hw - r0);       // pixels of the tile inside the frame
         const int n_chunk = n_valid - kChunk * warp;        // ... of this warp's chunk (may be <= 0)
         const T *lgw = static_cast<const T *>(p.logits) + (f * C * p.hw + r0 + kChunk * warp);

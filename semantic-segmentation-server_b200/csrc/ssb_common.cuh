@@ -150,6 +150,11 @@ __device__ __forceinline__ void bulk_copy_g2s_plain(void *dst_smem, const void *
                  : "memory");
 }
 
+// Asks L2 for [p, p + bytes) ahead of the loads that will want it (16-byte aligned address and size).
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
