@@ -98,7 +98,7 @@ SSB_API int ssb_preprocess_nearest_u8(const uint8_t *frames_bgr, int B, int Hc, 
  *   labels       [B][H][W] u8 label map (first index of the maximum, np.argmax semantics), written
  *                for the FULL frame; may be NULL to skip it
  *   stats        [B][C][4] u64, zeroed by the call, then accumulated
- * Limits: 2 <= C <= 255 (the fast path is compiled for C = 19 and C = 21), H*W < 2^31,
+ * Limits: 2 <= C <= 255 (the streaming fast path is compiled for every C from 2 to 32), H*W < 2^31,
  *         B*H*W < 2^40.  The fast path needs `logits` 16-byte aligned and `labels` 4-byte aligned
  *         (any torch allocation; a frame offset that is a multiple of 16 frames keeps both); other
  *         shapes/alignments take a slower generic kernel with identical results. */

@@ -101,6 +101,27 @@ def test_u8_shapes(ssb, shape):
     check_vs_oracle(ssb, q, max(1, shape[1] // 2), max(1, shape[2] - 1))
 
 
+@pytest.mark.parametrize("c", list(range(2, 34)))
+def test_u8_every_class_count_on_the_streaming_path(ssb, c, monkeypatch):
+    """The streaming kernel is compiled for every class count from 2 to 32 (32-, 64- or 128-bit shared-memory
+    loads by the parity of C); 33 takes the generic kernel.  Uniform scores, a narrow range with many ties, a
+    crop that cuts rows and columns, frames that do not end on tile boundaries -- and the same bytes from the
+    generic kernel."""
+    rng = np.random.default_rng(1000 + c)
+    b, h, w = int(rng.integers(2, 6)), int(rng.integers(40, 90)), int(rng.integers(37, 140))
+    q = rng.integers(0, 256, (b, h, w, c), dtype=np.uint8)
+    labels, stats = check_vs_oracle(ssb, q)
+    check_vs_oracle(ssb, q, h - 7, w - 5)
+    ties = rng.integers(0, 3, (b, h, w, c), dtype=np.uint8)
+    check_vs_oracle(ssb, ties, h, w - 1)
+    last = np.zeros((2, 64, 64, c), np.uint8)
+    last[..., c - 1] = 9                                # the maximum only in the last channel
+    check_vs_oracle(ssb, last)
+    monkeypatch.setenv("SSB_ARGMAX_CFG", "generic")
+    g_labels, g_stats = run_gpu(ssb, q)
+    assert (g_labels == labels).all() and (g_stats == stats).all()
+
+
 @pytest.mark.parametrize("shape", [(200, 8, 8, 21), (64, 3, 4, 21), (7, 4000, 4, 19), (5, 1, 3000, 21),
                                    (1000, 5, 5, 19), (3, 2, 1025, 21)])
 def test_u8_extreme_geometries_on_the_streaming_path(ssb, shape):
