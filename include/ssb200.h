@@ -258,6 +258,22 @@ SSB_API int ssb_fold_regions_host(int B, int C, int max_regions, const int32_t *
                                   const int32_t *parent, const int32_t *flags, const uint32_t *hist, const uint32_t *ring,
                                   int64_t *enclosed, int32_t *order, uint8_t *complete, int threads);
 
+/* ssb_contours_host: the reference's contour stage (sem_seg_server.py:88 cv2.findContours(RETR_TREE,
+ * CHAIN_APPROX_SIMPLE), :93-94 cv2.contourArea + area threshold, :115-122 cv2.moments + integer centroid) for the
+ * masks of B frames held on the host, a frame per pool thread.  Border following with marks (Suzuki & Abe) on the
+ * roi_h x roi_w crop of every mask; areas and moments are exact integer sums turned into doubles with OpenCV's
+ * constants, so every number equals what OpenCV returns, and the contours come in OpenCV's order.
+ *   masks_host    [B][H][W] u8, 0 = background (ssb_fg_mask_u8 output copied to the host)
+ *   n_candidates  [B] contours with area >= min_area and m00 != 0; more than max_candidates: the lists below are cut
+ *   cand_i32      [B][max_candidates][4] i32: is_hole, key, cx, cy -- key = first pixel (y*roi_w + x) of the region
+ *                 whose outer border this is / of the hole the border goes around (-1: not identified): the row of
+ *                 the region table that holds what the contour encloses; cx, cy = int(m10/m00), int(m01/m00)
+ *   cand_area     [B][max_candidates] f64 contourArea
+ *   n_contours    [B] all contours found (may be NULL) */
+SSB_API int ssb_contours_host(const uint8_t *masks_host, int B, int H, int W, int roi_h, int roi_w, double min_area,
+                              int max_candidates, int32_t *n_candidates, int32_t *cand_i32, double *cand_area,
+                              int32_t *n_contours, int threads);
+
 #ifdef __cplusplus
 }
 #endif

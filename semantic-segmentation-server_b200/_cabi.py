@@ -39,6 +39,8 @@ SIGNATURES = {
     "ssb_frames_to_device": (_c_int, [_c_void_p, _c_int, ctypes.c_size_t, _c_void_p, _c_void_p, _c_int, _c_void_p]),
     "ssb_fold_regions_host": (_c_int, [_c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p,
                                        _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_int]),
+    "ssb_contours_host": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, ctypes.c_double, _c_int, _c_void_p,
+                                   _c_void_p, _c_void_p, _c_void_p, _c_int]),
     "ssb_pipeline_create": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),
     "ssb_pipeline_destroy": (_c_int, [_c_void_p]),
     "ssb_pipeline_create_ingest": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),

@@ -183,3 +183,191 @@ extern "C" int ssb_fold_regions_host(int B, int C, int max_regions, const int32_
     });
     return SSB_OK;
 }
+
+// ---- contour stage of one frame: border following with marks (Suzuki & Abe), as cv2.findContours(RETR_TREE) ----
+// The reference calls cv2.findContours / contourArea / moments per frame (sem_seg_server.py:88, :93, :115-122).
+// cv2.findContours does not run in parallel on threads of a Python process; this restatement does (a frame per
+// pool thread).  It reproduces, on the ROI crop of a mask:
+//   * the borders OpenCV follows (8-connected foreground, outer and hole borders), in OpenCV's OUTPUT ORDER
+//     (pre-order of the border tree, siblings in reverse order of discovery) -- discovery depends on the marks a
+//     traced border leaves (a pixel whose right-hand neighbour was examined and found empty is marked negative
+//     and cannot start a hole border any more), so the marks are kept exactly;
+//   * contourArea and the moments m00, m10, m01 of every border: sums of products of integer coordinates, exact in
+//     64-bit integers, and independent of which collinear points CHAIN_APPROX_SIMPLE drops and of where on the
+//     border the point list starts; the final doubles are formed with OpenCV's own constants (0.5, 1/6).
+// Equality with OpenCV is a test (tests/test_hostpath.py: contour order, hole flags, start points of outer
+// borders, areas and centroids over > 10 000 random masks), not an assumption.
+namespace ssb {
+namespace {
+
+struct BorderInfo {
+    int parent, last_child, prev_sibling;   // tree over border numbers; children chained newest first
+    int start_x, start_y;                   // where the raster scan met the border
+    int key;                                // first pixel (y*w + x) of the region (outer) / of the hole (hole border), -1 unknown
+    bool is_hole;
+    long long a00, a10, a01;
+};
+
+struct ContourScratch {
+    std::vector<int> img;
+    std::vector<BorderInfo> borders;
+    std::vector<int> stack;
+};
+
+// Follows the border the raster scan met at pixel (x0, y0) of the ROI (unpadded coordinates; `img` is the
+// padded image, pixel (x, y) at img[(y + 1) * pitch + x + 1]) and numbers it `nbd`.
+void follow_border(int *img, int pitch, int x0, int y0, bool is_hole, int nbd, int w, BorderInfo &b) {
+    static const int dx[8] = {1, 1, 0, -1, -1, -1, 0, 1}, dy[8] = {0, -1, -1, -1, 0, 1, 1, 1};
+    int delta[16];
+    for (int s = 0; s < 16; ++s) delta[s] = dy[s & 7] * pitch + dx[s & 7];
+    int *i0 = img + (y0 + 1) * pitch + x0 + 1;
+    int s_end = is_hole ? 0 : 4, s = s_end;
+    int *i1;
+    do {
+        s = (s - 1) & 7;
+        i1 = i0 + delta[s];
+    } while (*i1 == 0 && s != s_end);
+    long long a00 = 0, a10 = 0, a01 = 0;
+    int y_min = y0, best_x = 1 << 30;      // hole borders: top row of the border, leftmost point of it with background below
+    if (*i1 == 0) {                         // an isolated pixel: a border of one point, all sums zero
+        *i0 = -nbd;
+    } else {
+        int *i3 = i0;
+        int x = x0, y = y0, prev_x = x0, prev_y = y0;
+        bool first = true;
+        y_min = 1 << 30;
+        for (;;) {
+            s_end = s;
+            int *i4;
+            for (;;) {
+                i4 = i3 + delta[++s];
+                if (*i4 != 0) break;
+            }
+            s &= 7;
+            if (static_cast<unsigned>(s - 1) < static_cast<unsigned>(s_end)) *i3 = -nbd;   // right-hand neighbour examined and empty
+            else if (*i3 == 1) *i3 = nbd;
+            // (x, y) is a point of the closed polygon
+            if (!first) {
+                const long long d = static_cast<long long>(prev_x) * y - static_cast<long long>(x) * prev_y;
+                a00 += d; a10 += d * (prev_x + x); a01 += d * (prev_y + y);
+            }
+            first = false;
+            if (is_hole) {
+                if (y < y_min) { y_min = y; best_x = 1 << 30; }
+                if (y == y_min && x < best_x && i3[pitch] == 0) best_x = x;
+            }
+            prev_x = x; prev_y = y;
+            if (i4 == i0 && i3 == i1) break;
+            i3 = i4;
+            x += dx[s]; y += dy[s];
+            s = (s + 4) & 7;
+        }
+        const long long d = static_cast<long long>(prev_x) * y0 - static_cast<long long>(x0) * prev_y;   // back to the first point
+        a00 += d; a10 += d * (prev_x + x0); a01 += d * (prev_y + y0);
+    }
+    b.a00 = a00; b.a10 = a10; b.a01 = a01;
+    b.key = !is_hole ? y0 * w + x0 : (best_x < (1 << 30) ? (y_min + 1) * w + best_x : -1);
+}
+
+// All borders of one ROI (h x w, row pitch `ld` bytes), in OpenCV's output order, into sc.borders / `out_order`.
+void frame_borders(const uint8_t *mask, int h, int w, int ld, ContourScratch &sc, std::vector<int> &out_order) {
+    const int pitch = w + 2;
+    sc.img.assign(static_cast<size_t>(h + 2) * pitch, 0);
+    for (int y = 0; y < h; ++y) {
+        const uint8_t *m = mask + static_cast<size_t>(y) * ld;
+        int *row = sc.img.data() + static_cast<size_t>(y + 1) * pitch + 1;
+        for (int x = 0; x < w; ++x) row[x] = m[x] != 0;
+    }
+    sc.borders.clear();
+    sc.borders.push_back(BorderInfo{});          // 0: unused
+    BorderInfo frame{};                          // 1: the frame, a hole border, root of the tree
+    frame.parent = 0; frame.last_child = 0; frame.prev_sibling = 0; frame.is_hole = true;
+    sc.borders.push_back(frame);
+    int *img = sc.img.data();
+    for (int y = 0; y < h; ++y) {
+        int lnbd = 1;
+        int *row = img + static_cast<size_t>(y + 1) * pitch + 1;
+        for (int x = 0; x < w; ++x) {
+            int f = row[x];
+            if (f == 0) continue;
+            int start = -1;                      // 0: outer border starts here, 1: hole border
+            if (f == 1 && row[x - 1] == 0) {
+                start = 0;
+            } else if (f >= 1 && row[x + 1] == 0) {
+                start = 1;
+                if (f > 1) lnbd = f;
+            }
+            if (start >= 0) {
+                const int nbd = static_cast<int>(sc.borders.size());
+                const BorderInfo &prev = sc.borders[lnbd];
+                BorderInfo b{};
+                b.is_hole = start == 1;
+                // Suzuki & Abe, table 1: same kind as the last border met on this row -> its parent; else that border
+                b.parent = b.is_hole == prev.is_hole ? prev.parent : lnbd;
+                b.start_x = x; b.start_y = y;
+                b.last_child = 0;
+                b.prev_sibling = sc.borders[b.parent].last_child;
+                sc.borders.push_back(b);
+                sc.borders[b.parent].last_child = nbd;
+                follow_border(img, pitch, x, y, start == 1, nbd, w, sc.borders[nbd]);
+                f = row[x];
+            }
+            if (f != 1) lnbd = f < 0 ? -f : f;
+        }
+    }
+    // pre-order of the tree, children newest first
+    out_order.clear();
+    sc.stack.clear();
+    for (int c = sc.borders[1].last_child; c; c = sc.borders[c].prev_sibling) sc.stack.push_back(c);
+    // the stack pops the LAST pushed first: push siblings oldest-first so that the newest comes out first
+    std::reverse(sc.stack.begin(), sc.stack.end());
+    while (!sc.stack.empty()) {
+        const int n = sc.stack.back();
+        sc.stack.pop_back();
+        out_order.push_back(n);
+        const size_t at = sc.stack.size();
+        for (int c = sc.borders[n].last_child; c; c = sc.borders[c].prev_sibling) sc.stack.push_back(c);
+        std::reverse(sc.stack.begin() + at, sc.stack.end());
+    }
+}
+
+}  // namespace
+}  // namespace ssb
+
+extern "C" int ssb_contours_host(const uint8_t *masks_host, int B, int H, int W, int roi_h, int roi_w, double min_area,
+                                 int max_candidates, int32_t *n_candidates, int32_t *cand_i32, double *cand_area,
+                                 int32_t *n_contours, int threads) {
+    using namespace ssb;
+    if (B < 0 || H <= 0 || W <= 0 || roi_h < 1 || roi_h > H || roi_w < 1 || roi_w > W || max_candidates < 1)
+        return fail(SSB_ERR_BAD_SHAPE, "bad shape B=%d H=%d W=%d ROI (%d,%d) max_candidates=%d", B, H, W, roi_h, roi_w, max_candidates);
+    if (B == 0) return SSB_OK;
+    if (!masks_host || !n_candidates || !cand_i32 || !cand_area) return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
+    pool().run(B, threads, [&](int b) {
+        thread_local ContourScratch sc;
+        thread_local std::vector<int> order;
+        frame_borders(masks_host + static_cast<size_t>(b) * H * W, roi_h, roi_w, W, sc, order);
+        if (n_contours) n_contours[b] = static_cast<int32_t>(order.size());
+        int n = 0;
+        for (int nbd : order) {
+            const BorderInfo &c = sc.borders[nbd];
+            // cv2.contourArea: |sum of cross products| / 2;  cv2.moments: m00 = a00/2, m10 = a10/6, m01 = a01/6 with the
+            // sign of a00 folded into the constants -- the same doubles, from exact integer sums
+            double a00 = static_cast<double>(c.a00);
+            const double area = (a00 < 0 ? -a00 : a00) * 0.5;
+            if (area < min_area) continue;                               // sem_seg_server.py:94
+            if (c.a00 == 0) continue;                                    // m00 == 0, sem_seg_server.py:117
+            const double db1_2 = c.a00 > 0 ? 0.5 : -0.5, db1_6 = c.a00 > 0 ? 0.16666666666666666666666666666667 : -0.16666666666666666666666666666667;
+            const double m00 = a00 * db1_2, m10 = static_cast<double>(c.a10) * db1_6, m01 = static_cast<double>(c.a01) * db1_6;
+            if (n < max_candidates) {
+                int32_t *o = cand_i32 + (static_cast<size_t>(b) * max_candidates + n) * 4;
+                o[0] = c.is_hole; o[1] = c.key;
+                o[2] = static_cast<int32_t>(m10 / m00);                  // int(M['m10'] / M['m00']), sem_seg_server.py:121
+                o[3] = static_cast<int32_t>(m01 / m00);
+                cand_area[static_cast<size_t>(b) * max_candidates + n] = area;
+            }
+            ++n;
+        }
+        n_candidates[b] = n;                                             // > max_candidates: the list is cut short
+    });
+    return SSB_OK;
+}

@@ -390,6 +390,36 @@ def fold_regions_batch(tables_host, threads=8, scratch=None):
     return out
 
 
+def contour_candidates_batch(masks_host, roi_h, roi_w, min_area, threads=8, max_candidates=64, scratch=None):
+    """The reference's contour stage (sem_seg_server.py:88, :93-94, :115-122) for a batch of masks on the host
+    (numpy [B,H,W] u8), natively and a frame per thread (C-ABI: ssb_contours_host): per frame the list of
+    (is_hole, key, area, cx, cy) of the contours that pass the area threshold, in OpenCV's contour order --
+    what contour_worker.contour_candidates computes with cv2.  A frame with more than `max_candidates`
+    candidates comes back as None."""
+    m = masks_host
+    if not (isinstance(m, np.ndarray) and m.dtype == np.uint8 and m.ndim == 3 and m.flags.c_contiguous):
+        raise ValueError("masks_host must be a C-contiguous [B,H,W] uint8 array")
+    b, h, w = m.shape
+    scratch = {} if scratch is None else scratch
+    if scratch.get("cand_shape") != (b, max_candidates):
+        scratch.update(cand_shape=(b, max_candidates), n=np.empty((b,), np.int32), ci=np.empty((b, max_candidates, 4), np.int32),
+                       ca=np.empty((b, max_candidates), np.float64))
+    n, ci, ca = scratch["n"], scratch["ci"], scratch["ca"]
+    _cabi.check(_cabi.lib.ssb_contours_host(m.ctypes.data, b, h, w, roi_h, roi_w, float(min_area), max_candidates,
+                                            n.ctypes.data, ci.ctypes.data, ca.ctypes.data, None, threads))
+    out = []
+    for i in range(b):
+        k = int(n[i])
+        if k > max_candidates:
+            out.append(None)
+        elif k == 0:
+            out.append([])
+        else:
+            rows, areas = ci[i, :k].tolist(), ca[i, :k].tolist()
+            out.append([(r[0], r[1] if r[1] >= 0 else None, a, r[2], r[3]) for r, a in zip(rows, areas)])
+    return out
+
+
 def frames_to_device(frames, dst, staging=None, threads=8, stream=None):
     """The frames cap.read() returned (a list of equally shaped C-contiguous uint8 arrays) -> dst[:len(frames)]
     (device tensor [B,Hc,Wc,3]) on `stream` (C-ABI: ssb_frames_to_device).  Frames in page-locked memory are

@@ -114,8 +114,7 @@ _workers = None
 def _contour_workers(n_workers, slot_bytes):
     """The process-wide contour worker pool (started on first use, restarted when a larger batch arrives)."""
     global _workers
-    n_workers = CONTOUR_WORKERS if n_workers is None else n_workers
-    if n_workers <= 0:
+    if not n_workers or n_workers <= 0:
         return None
     if _workers is None or _workers.slot_bytes < slot_bytes or len(_workers._procs) != n_workers:
         if _workers is not None:
@@ -133,6 +132,20 @@ def _contour_pool():
     return _pool
 
 
+_buffers = {}
+
+
+def _feeder_buffers(dev, slot, shape):
+    """Page-locked staging + device input buffer of a feeder slot, kept for the life of the process (locking
+    hundreds of MB takes ~0.1 s: not something to repeat per call of recognize_and_segment)."""
+    key = (str(dev), slot, tuple(shape))
+    if key not in _buffers:
+        for k in [k for k in _buffers if k[:2] == key[:2]]:      # another frame size took this slot before
+            del _buffers[k]
+        _buffers[key] = (torch.empty(shape, dtype=torch.uint8).pin_memory(), torch.empty(shape, dtype=torch.uint8, device=dev))
+    return _buffers[key]
+
+
 def _open_camera(camera_idx):
     if hasattr(camera_idx, "read"):
         return camera_idx
@@ -148,7 +161,8 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
     try:
         stream = torch.cuda.Stream(dev)
         pinned, busy = [None, None], [None, None]      # two frame buffers and the event of their last transfer
-        device_in, held = [None, None], [None, None]
+        device_in, held, consumed = [None, None], [None, None], [None, None]
+        up_stream = torch.cuda.Stream(dev)
         geom, k = None, 0
         tables = [None] * 4
         while cap.isOpened() and not stop.is_set():
@@ -167,18 +181,24 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
             if busy[slot] is not None:
                 busy[slot].synchronize()               # the transfer that last read this slot's buffers has finished
             if pinned[slot] is None or pinned[slot].shape[1:] != (cam_h, cam_w, 3):
-                pinned[slot] = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8).pin_memory()
-                device_in[slot] = torch.empty((batch_frames, cam_h, cam_w, 3), dtype=torch.uint8, device=dev)
+                pinned[slot], device_in[slot] = _feeder_buffers(dev, slot, (batch_frames, cam_h, cam_w, 3))
             frames = [f if (f.dtype == np.uint8 and f.flags.c_contiguous) else np.ascontiguousarray(f, np.uint8) for f in frames]
             held[slot] = frames                        # frames in page-locked memory are read by the DMA where they are
+            # Uploads have a stream of their own: on the kernels' stream the copy of batch k+1 would wait for the
+            # kernels of batch k.  It waits only for the pre-process kernel that last read this slot's device buffer.
+            if consumed[slot] is not None:
+                up_stream.wait_event(consumed[slot])
+            # native: pageable frames are gathered into the pinned buffer by host threads and sent frame by
+            # frame (gather and DMA overlap), page-locked ones go straight from their own memory
+            batch = hotpath.frames_to_device(frames, device_in[slot], pinned[slot], threads=HOST_THREADS,
+                                             stream=up_stream)[:len(frames)]
+            busy[slot] = torch.cuda.Event()
+            busy[slot].record(up_stream)
             with torch.cuda.stream(stream):
-                # native: pageable frames are gathered into the pinned buffer by host threads and sent frame by
-                # frame (gather and DMA overlap), page-locked ones go straight from their own memory
-                batch = hotpath.frames_to_device(frames, device_in[slot], pinned[slot], threads=HOST_THREADS,
-                                                 stream=stream)[:len(frames)]
-                busy[slot] = torch.cuda.Event()
-                busy[slot].record(stream)
+                stream.wait_event(busy[slot])
                 inputs = hotpath.preprocess_frames(batch, geom)                   # :150-161
+                consumed[slot] = torch.cuda.Event()
+                consumed[slot].record(stream)
                 logits, scale, zero_point = engine.run_logits(inputs)             # :162 (model, upstream)
                 nchw = getattr(engine, "layout", "nhwc") == "nchw"
                 if nchw:                                                          # :163-170, :102-122
@@ -211,8 +231,9 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
 
     Two stages run side by side: a feeder thread gathers batch n+1 and enqueues its GPU work while this
     thread reads back batch n, runs the OpenCV tails and pushes the objects -- in frame order, so the deque
-    looks exactly as the reference's.  `contour_workers`: processes for the OpenCV contour stage (None: as
-    many as CONTOUR_WORKERS; 0: in this process, on threads)."""
+    looks exactly as the reference's.  `contour_workers`: where the contour stage (sem_seg_server.py:88-122)
+    runs -- None: the library's own border following on host threads (same contours and numbers as OpenCV);
+    k > 0: cv2 in k worker processes; 0: cv2 in this process."""
     import queue
     import threading
     segmented_objects.clear()
@@ -236,7 +257,7 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
             if isinstance(item, BaseException):
                 raise item
             n_frames, geom, res, ready = item
-            workers = _contour_workers(contour_workers, batch_frames * height * width) if mode == "contours" else None
+            workers = _contour_workers(contour_workers, batch_frames * height * width) if mode == "contours" and contour_workers else None
             with torch.cuda.stream(copy_stream):
                 copy_stream.wait_event(ready)
                 if mode == "contours" and workers is not None:
@@ -264,14 +285,21 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
                     return hotpath.objects_from_regions(
                         masks_h[i], enclosed[i], segment_centroid_min_area, labels,
                         label_map=lambda: label_maps[i, :geom.roi_h, :geom.roi_w].cpu().numpy())
-                if workers is not None:
-                    # findContours / contourArea / moments ran in the worker processes (cv2.findContours does not
-                    # run in parallel on threads); here the candidates meet the region tables, in frame order
-                    candidates = workers.collect()
-                    per_frame = [contour_pool.objects_from_candidates(candidates[i], enclosed[i], labels) for i in range(n_frames)]
-                    per_frame = [contour_tail(i) if objs is None else objs for i, objs in enumerate(per_frame)]
+                if contour_workers == 0:
+                    per_frame = list(_contour_pool().map(contour_tail, range(n_frames)))     # cv2, in this process
                 else:
-                    per_frame = list(_contour_pool().map(contour_tail, range(n_frames)))
+                    if workers is not None:
+                        # cv2.findContours / contourArea / moments ran in the worker processes
+                        candidates = workers.collect()
+                    else:
+                        # the same contours, areas and centroids from the library's border following (equal to
+                        # OpenCV's, tests/test_hostpath.py), a frame per host thread
+                        candidates = hotpath.contour_candidates_batch(tables_h["mask"][:n_frames], geom.roi_h, geom.roi_w,
+                                                                      segment_centroid_min_area, HOST_THREADS, scratch=fold_scratch)
+                    # the candidates meet the region tables, in frame order
+                    per_frame = [None if candidates[i] is None else
+                                 contour_pool.objects_from_candidates(candidates[i], enclosed[i], labels) for i in range(n_frames)]
+                    per_frame = [contour_tail(i) if objs is None else objs for i, objs in enumerate(per_frame)]
             else:
                 shift = hotpath._cabi.F16_FIXED_SHIFT if res["float_scores"] else 0
                 per_frame = [hotpath.objects_from_stats(stats_h[i], width, height, labels, min_area_ratio, res["scale"],

@@ -105,3 +105,54 @@ def test_contour_worker_processes_give_the_in_process_objects():
                     assert cp.objects_from_candidates(cands[i], None, NAMES) is None
     finally:
         workers.close()
+
+
+def _random_masks(rng, n, h, w, rep):
+    import cv2
+    out = np.zeros((n, h, w), np.uint8)
+    for i in range(n):
+        kind = (i + rep) % 5
+        if kind == 0:
+            m = rng.random((h, w)) < rng.uniform(0.1, 0.9)
+        elif kind == 1:
+            cell = int(rng.integers(2, 7))
+            m = np.kron(rng.random((h // cell + 1, w // cell + 1)) < 0.5, np.ones((cell, cell)))[:h, :w] > 0
+        elif kind == 2:
+            m = np.zeros((h, w), bool)
+            for r in range(0, min(h, w) // 2, int(rng.integers(1, 4))):
+                m[r:h - r, r:w - r] = r % 2 == 0
+            m ^= rng.random((h, w)) < 0.04
+        elif kind == 3:
+            m = cv2.dilate((rng.random((h, w)) < 0.4).astype(np.uint8), np.ones((2, 2), np.uint8)) > 0
+        else:
+            m = rng.random((h, w)) >= 0.15
+        out[i] = m * 255
+    return out
+
+
+def test_native_contour_stage_equals_opencv_on_ten_thousand_masks():
+    """cv2.findContours(RETR_TREE, CHAIN_APPROX_SIMPLE) + contourArea + moments against the library's border
+    following: the same contours in the same order, the same outer / hole flags and region keys, and areas and
+    centroids equal as doubles / integers -- over noise of every density, blocks, nested rings with specks,
+    dilated noise (thin walls) and nearly full frames, at random ROI sizes from 1x1 up."""
+    import importlib
+    import ssb200
+    cw = importlib.import_module(ssb200.__name__ + ".contour_worker")
+    rng = np.random.default_rng(5)
+    H, W = 48, 64
+    frames = contours = 0
+    for rep in range(65):
+        h, w = int(rng.integers(1, H + 1)), int(rng.integers(1, W + 1))
+        masks = np.full((80, H, W), 255, np.uint8)              # whatever lies outside the ROI must not matter
+        masks[:, :h, :w] = _random_masks(rng, 80, h, w, rep)
+        for min_area in (0.0, 6.5):
+            got = ssb200.contour_candidates_batch(masks, h, w, min_area, threads=3, max_candidates=2048)
+            for i in range(80):
+                want = [c[:5] for c in cw.contour_candidates(masks[i, :h, :w], min_area)]
+                assert got[i] == want, (rep, i, h, w, min_area)
+                contours += len(want)
+            frames += 80
+    assert frames >= 10000 and contours > 50000
+    # a cut-short candidate list is reported, not silently truncated
+    noisy = _random_masks(rng, 2, H, W, 0)
+    assert ssb200.contour_candidates_batch(noisy, H, W, 0.0, max_candidates=3) == [None, None]
