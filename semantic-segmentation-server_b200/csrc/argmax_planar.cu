@@ -382,7 +382,20 @@ __global__ void __launch_bounds__(NWARPS * 32, MINB) argmax_stats_planar_kernel(
             y_base = fastdiv(static_cast<uint32_t>(r0), p.divw);
             k = 0;
         }
-#if SSB_PLANAR_PREFETCH
+#if SSB_PLANAR_PREFETCH == 2
+        // per-thread L2 prefetches of the words this thread will load in the next tile (same frame, full tile)
+        if (t + 1 < t1 && i + 1 < p.tiles_per_frame && (i + 2) * kTilePx <= p.hw) {
+            const char *q = reinterpret_cast<const char *>(static_cast<const T *>(p.logits) + (f * C * p.hw + r0 + kTilePx + kChunk * warp)) +
+                            lane * (P::kBytes == 2 ? 4 : 4);
+            const long long plane_bytes = static_cast<long long>(p.hw) * P::kBytes;
+#pragma unroll
+            for (int c = 0; c < C; ++c, q += plane_bytes) {
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(q + 128 * jj));
+            }
+        }
+#elif SSB_PLANAR_PREFETCH
         // The C plane chunks this warp reads in the NEXT tile are requested from DRAM now (one bulk prefetch into
         // L2 per plane, issued by one lane): a thread holds all its loads of a tile in registers, so it cannot
         // have two tiles in flight itself, and with four warps per scheduler DRAM latency was not covered.
