@@ -122,7 +122,7 @@ SSB_API int ssb_argmax_stats_f16(const uint16_t *logits, int B, int H, int W, in
  *         pixel of the real sum; |value| < 2^39.
  *   _f16: 16-bit halves as uint16_t bit patterns; SQ = sum of value * 2^24, exact (finite winners).
  * `logits` needs element alignment only (fp16 loads pixel pairs when it is 4-byte aligned); `labels`
- * may have any alignment.  C = 19 and 21 run the unrolled kernel, other class counts a generic one. */
+ * may have any alignment.  Class counts from 2 to 32 run an unrolled kernel, larger ones a generic one. */
 SSB_API int ssb_argmax_stats_nchw_f32(const float *logits, int B, int H, int W, int C, int roi_h, int roi_w,
                               uint8_t *labels, uint64_t *stats, void *stream);
 SSB_API int ssb_argmax_stats_nchw_f16(const uint16_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,

@@ -193,3 +193,21 @@ def test_argument_errors(ssb):
         ssb.argmax_stats_nchw(x.permute(0, 2, 3, 1))          # not contiguous
     with pytest.raises(ValueError):
         ssb.argmax_stats_nchw(x.to(torch.float64))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float16])
+@pytest.mark.parametrize("c", list(range(2, 34)))
+def test_every_class_count(ssb, dtype, c, monkeypatch):
+    """The unrolled planar kernels are compiled for every class count from 2 to 32 (33: the generic kernel).  Odd
+    H*W so that planes alternate between even and odd element phases (the fp16 pair loads), a crop that cuts rows and
+    columns, many ties; and the same bytes from the generic kernel."""
+    rng = np.random.default_rng(500 + c)
+    b, h, w = int(rng.integers(2, 5)), int(rng.integers(35, 80)) | 1, int(rng.integers(41, 120)) | 1
+    x = (rng.standard_normal((b, c, h, w)) * 3).astype(dtype)
+    labels, stats = check(ssb, x)
+    check(ssb, x, h - 6, w - 3)
+    ties = rng.integers(-1, 2, (b, c, h, w)).astype(dtype)
+    check(ssb, ties, h, w - 1)
+    monkeypatch.setenv("SSB_ARGMAX_NCHW_CFG", "generic")
+    g_labels, g_stats = run_gpu(ssb, x)
+    assert (g_labels == labels).all() and (g_stats == stats).all()
