@@ -105,7 +105,7 @@ SSB_API int ssb_preprocess_nearest_u8(const uint8_t *frames_bgr, int B, int Hc, 
 SSB_API int ssb_argmax_stats_u8(const uint8_t *logits, int B, int H, int W, int C, int roi_h, int roi_w,
                         uint8_t *labels, uint64_t *stats, void *stream);
 
-/* Same contract for IEEE fp16 logits (Cityscapes-shaped config).  `logits` is [B][H][W][C] of
+/* Same contract for IEEE fp16 logits (Cityscapes-shaped config; streaming fast path for 2 <= C <= 32).  `logits` is [B][H][W][C] of
  * 16-bit halves passed as uint16_t bit patterns.  Comparison is the floating-point `>` (so
  * -0 == +0 and the first index wins); inputs must be NaN-free (a NaN never wins here, numpy
  * lets the first NaN win).  SQ accumulates value * 2^24 exactly; +-inf winners are not supported

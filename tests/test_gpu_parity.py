@@ -301,6 +301,22 @@ def test_f16_shapes(ssb, shape):
 
 
 # ---- K1 pre-process ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("c", list(range(2, 34)))
+def test_f16_every_class_count_on_the_streaming_path(ssb, c, monkeypatch):
+    """fp16 scores, every class count the streaming kernel is compiled for (2..32; 33: generic kernel): normal
+    scores, ties with both zeros, a crop; and the same bytes from the generic kernel."""
+    rng = np.random.default_rng(2000 + c)
+    b, h, w = int(rng.integers(2, 5)), int(rng.integers(40, 80)), int(rng.integers(37, 120))
+    x = (rng.standard_normal((b, h, w, c)) * 4).astype(np.float16)
+    labels, stats = check_vs_oracle(ssb, x)
+    check_vs_oracle(ssb, x, h - 7, w - 5)
+    ties = rng.choice(np.array([-1.0, -0.0, 0.0, 1.0], np.float16), size=(b, h, w, c))
+    check_vs_oracle(ssb, ties, h, w - 1)
+    monkeypatch.setenv("SSB_ARGMAX_F16_CFG", "generic")
+    g_labels, g_stats = run_gpu(ssb, x)
+    assert (g_labels == labels).all() and (g_stats == stats).all()
+
+
 @pytest.mark.parametrize("shape", [(200, 8, 8, 19), (64, 3, 4, 21), (7, 4000, 4, 19), (5, 1, 3000, 21),
                                    (600, 5, 5, 19), (3, 2, 1025, 21)])
 def test_f16_extreme_geometries_on_the_streaming_path(ssb, shape):
