@@ -263,6 +263,8 @@ SSB_API int ssb_fold_regions_host(int B, int C, int max_regions, const int32_t *
  * masks of B frames held on the host, a frame per pool thread.  Border following with marks (Suzuki & Abe) on the
  * roi_h x roi_w crop of every mask; areas and moments are exact integer sums turned into doubles with OpenCV's
  * constants, so every number equals what OpenCV returns, and the contours come in OpenCV's order.
+ * (Equality with OpenCV holds while the moment sums stay below 2^53, where OpenCV's own double accumulation is
+ * exact: ROIs up to about 2000 x 2000.)
  *   masks_host    [B][H][W] u8, 0 = background (ssb_fg_mask_u8 output copied to the host)
  *   n_candidates  [B] contours with area >= min_area and m00 != 0; more than max_candidates: the lists below are cut
  *   cand_i32      [B][max_candidates][4] i32: is_hole, key, cx, cy -- key = first pixel (y*roi_w + x) of the region

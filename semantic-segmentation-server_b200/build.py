@@ -49,7 +49,7 @@ def build_library(force=False, verbose=False):
             sys.stderr.write(r.stdout + r.stderr)
         if r.returncode:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
-    with ThreadPoolExecutor(max_workers=4) as ex:
+    with ThreadPoolExecutor(max_workers=max(4, min(16, os.cpu_count() or 4))) as ex:
         list(ex.map(run, jobs))
     if jobs or not os.path.exists(LIB) or any(os.path.getmtime(o) > os.path.getmtime(LIB) for o in objs):
         run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
