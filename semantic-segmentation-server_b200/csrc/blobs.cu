@@ -328,8 +328,8 @@ extern "C" int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, i
                 fprintf(stderr, "blob_cluster_kernel: %d threads, %zu B shared memory, %d clusters of %d active at once\n",
                         kStripThreads, smem, n_clusters, kStrips);
             }
-            SSB_CUDA_TRY(cudaLaunchKernelEx(&cfg, blob_cluster_kernel, sp));
-            return SSB_OK;
+            if (cudaLaunchKernelEx(&cfg, blob_cluster_kernel, sp) == cudaSuccess) return SSB_OK;
+            cudaGetLastError();   // a device / context that cannot place the cluster: the global-memory kernels below
         }
     }
     SSB_CUDA_TRY(cudaMemsetAsync(count, 0, sizeof(int) * B, st));
