@@ -25,6 +25,9 @@
 namespace ssb {
 namespace {
 
+#ifndef SSB_PRE_TRIGGER
+#define SSB_PRE_TRIGGER 0   // tuning: 1 = let the next kernel's CTAs be placed from the top of every CTA, 2 = once its row is read
+#endif
 #ifndef SSB_PRE_WARPS
 #define SSB_PRE_WARPS 2   // warps per CTA: 1 -> 35.0 us, 2 -> 29.0, 4 -> 29.8, 8 -> 32.5 (64 frames of 1080p)
 #endif
@@ -42,6 +45,9 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
                           const int *__restrict__ xtab, const int *__restrict__ ytab, int new_w, int new_h,
                           uint8_t *__restrict__ out, int H, int W, int rows_total, int src_bytes, int dst_bytes) {
     extern __shared__ __align__(16) uint8_t smem[];
+#if SSB_PRE_TRIGGER == 1
+    pdl_trigger();
+#endif
     pdl_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row = blockIdx.x * kPreWarps + warp;          // flat (frame, output row)
@@ -84,6 +90,9 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
     }
     cp_async_wait_all();
     __syncwarp();
+#if SSB_PRE_TRIGGER == 2
+    pdl_trigger();   // this warp's reads are done
+#endif
 
     // 2. gather: quads of output pixels -> three packed words each
     auto do_quad = [&](int q, const int4 &t) {
