@@ -1,7 +1,7 @@
 """B200-native hot path of goruck/semantic-segmentation-server: frame pre-process, logits -> label
 map, per-label segment statistics.  Host code in Python, kernels in libssb200.so (C-ABI, CUDA
 sm_100a).  Importing this package loads the library and fails if it is not built."""
-from . import _cabi, hotpath, scheduler  # noqa: F401
+from . import _cabi, contour_pool, hotpath, scheduler  # noqa: F401
 from .hotpath import (Centroid, FrameGeometry, HostPipeline, HostStaging, IngestPipeline, SegmentContour, argmax_stats,  # noqa: F401
                       argmax_stats_nchw, blob_regions, contour_candidates_batch, fold_region_histograms, fold_regions_batch, frames_to_device,
                       objects_from_regions,
