@@ -126,9 +126,17 @@ extern "C" int ssb_frames_to_device(const uint8_t *const *frames_host, int n, si
     };
     int dev = 0;
     SSB_CUDA_TRY(cudaGetDevice(&dev));
-    // direct frames first (no host work), then the gathered ones as their copies finish
-    for (int i = 0; i < n; ++i)
-        if (direct[i]) send(i);
+    // direct frames first (no host work; frames that follow each other in memory go as one copy), then the
+    // gathered ones as their copies finish
+    for (int i = 0; i < n;) {
+        if (!direct[i]) { ++i; continue; }
+        int j = i + 1;
+        while (j < n && direct[j] && frames_host[j] == frames_host[j - 1] + frame_bytes) ++j;
+        if (cudaMemcpyAsync(dst_device + frame_bytes * i, frames_host[i], frame_bytes * (j - i), cudaMemcpyHostToDevice, st) !=
+            cudaSuccess)
+            failed.store(1);
+        i = j;
+    }
     if (n_staged) {
         std::vector<int> todo;
         for (int i = 0; i < n; ++i)
