@@ -126,18 +126,21 @@ def warm_cpu_port(batch_np, threads, out, seconds=CPU_WARM_SECONDS, min_passes=1
     return n
 
 
-def time_cpu_port(batch_np, threads, min_seconds, max_passes=1000):
-    """Oracle C port (oracle/segpath_c.c), frames handed to `threads` pooled host threads."""
+def time_cpu_port(batches_np, threads, min_seconds, max_passes=1000):
+    """Oracle C port (oracle/segpath_c.c), frames handed to `threads` pooled host threads; the batches alternate
+    as in the `--impl reference` arm (re-reading ONE 354 MB batch leaves part of it in a large last-level cache
+    and reads ~15 % faster)."""
     from oracle import cport
     out = _cpu_port_outputs()
-    warm_cpu_port(batch_np, threads, out)
+    for b in batches_np:
+        warm_cpu_port(b, threads, out, CPU_WARM_SECONDS / len(batches_np))
     passes, t0 = 0, time.perf_counter()
     while True:
-        cport.argmax_stats(batch_np, ROI_H, ROI_W, threads=threads, out=out)
+        cport.argmax_stats(batches_np[passes % len(batches_np)], ROI_H, ROI_W, threads=threads, out=out)
         passes += 1
         el = time.perf_counter() - t0
         if el >= min_seconds or passes >= max_passes:
-            return passes * batch_np.shape[0] / el, passes, el
+            return passes * batches_np[0].shape[0] / el, passes, el
 
 
 def run_reference(args):
@@ -233,8 +236,10 @@ def time_reference_literal(seconds_per_leg=4.0):
             "scenes; 1 process for %.0f s, then %d processes x %d passes" % (seconds_per_leg, cores, repeat)}
 
 
-def reference_literal_in_child():
-    r = subprocess.run([sys.executable, os.path.abspath(__file__), "--leg", "reference_literal"],
+def cpu_leg_in_child(leg):
+    """Runs one of the CPU legs in a child process of its own (no CUDA context, no threads of this process
+    beside it: the conditions of the `--impl reference` arm)."""
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), "--leg", leg],
                        capture_output=True, text=True, timeout=600)
     for line in reversed(r.stdout.strip().splitlines()):
         if line.startswith("{"):
@@ -699,12 +704,11 @@ def run_ssb(args):
         achieved = ALGO_BYTES_PER_FRAME * BATCH / launch_s / 1e9
         e2e_fps = world * BATCH * e2e_steps / (e2e_ms * 1e-3)
         threads = cpu_threads()
-        cpu_fps, passes, cpu_el = time_cpu_port(host_batches[0], threads, min_seconds=10.0)
-        t1 = time.perf_counter()
-        from oracle import segpath as sp
-        sp.argmax_stats(host_batches[0][:2], ROI_H, ROI_W)
-        numpy_fps = 2 / (time.perf_counter() - t1)
-        literal = reference_literal_in_child()
+        port = cpu_leg_in_child("cpu_port")
+        cpu_fps, passes, cpu_el, numpy_fps = (port.get(k) for k in ("value", "passes", "seconds", "numpy_fps"))
+        if cpu_fps is None:
+            raise SystemExit("bench: CPU baseline leg failed: %s" % port.get("error"))
+        literal = cpu_leg_in_child("reference_literal")
         reply["reference_literal_cpu_frames_per_s"] = {"one_core": literal.get("one_core"), "all_cores": literal.get("value"),
                                                        "cores": literal.get("cores")}
         traffic, traffic_src = None, None
@@ -735,7 +739,7 @@ def run_ssb(args):
                          "algorithmic_bytes_per_launch": ALGO_BYTES_PER_FRAME * BATCH,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "cpu_baseline": {"value": cpu_fps, "unit": "frames/s", "cores": threads, "kind": "port",
-                             "sample": "%d passes over one %d-frame batch in %.1f s, C port, %d pooled threads; "
+                             "sample": "child process: %d passes over two alternating %d-frame batches in %.1f s, C port, %d pooled threads; "
                                        "numpy restatement 1 thread: %.1f frames/s" % (passes, BATCH, cpu_el, threads,
                                                                                        numpy_fps),
                              "reference_literal": literal},
@@ -773,6 +777,13 @@ def main():
     args = ap.parse_args()
     if args.leg == "reference_literal":
         print(json.dumps(time_reference_literal()))
+    elif args.leg == "cpu_port":
+        batches = [synth_batch(1000 + i) for i in range(2)]
+        fps, passes, el = time_cpu_port(batches, cpu_threads(), min_seconds=10.0)
+        t1 = time.perf_counter()
+        from oracle import segpath as sp
+        sp.argmax_stats(batches[0][:2], ROI_H, ROI_W)
+        print(json.dumps({"value": fps, "passes": passes, "seconds": el, "numpy_fps": 2 / (time.perf_counter() - t1)}))
     elif args.impl == "reference":
         run_reference(args)
     else:
