@@ -162,6 +162,12 @@ def run_reference(args):
         cport.argmax_stats(batches[i % 2], ROI_H, ROI_W, threads=threads, out=out)
     el = time.perf_counter() - t0
     fps = args.steps * BATCH / el
+    more = []                                   # how much the figure moves: the same K-step region five more times
+    for _ in range(5):
+        t1 = time.perf_counter()
+        for i in range(args.steps):
+            cport.argmax_stats(batches[i % 2], ROI_H, ROI_W, threads=threads, out=out)
+        more.append(args.steps * BATCH / (time.perf_counter() - t1))
     sample = "%d steps x one %d-frame batch (2 batches alternating), C port of np.argmax+bincount stats, %d pooled threads" % (
         args.steps, BATCH, threads)
     print(json.dumps({
@@ -169,7 +175,8 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": CONFIG,
-        "timing": {"warmup_steps_run": n_warm, "timed_region_s": el},
+        "timing": {"warmup_steps_run": n_warm, "timed_region_s": el,
+                   "frames_per_s_of_5_more_regions": {"min": min(more), "median": float(np.median(more)), "max": max(more)}},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
