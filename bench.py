@@ -447,15 +447,16 @@ def reply_e2e(ssb200, torch, n_frames=2048, batch=64):
     cam = torch.randint(0, 256, (8, CAM_H, CAM_W, 3), dtype=torch.uint8, generator=g).pin_memory().numpy()
     engine = FixedScores(torch, batch)
     names = {i: "label%d" % i for i in range(C)}
-    dt = None
-    for n in (4 * batch, n_frames):                       # first pass: allocations, thread pools, lazy module loads
+    rates = []
+    for n in (4 * batch, n_frames, n_frames, n_frames):   # first pass: allocations, thread pools, lazy module loads
         camera = srv.ArrayCamera([cam[i % 8] for i in range(n)])
         t0 = time.perf_counter()
         srv.recognize_and_segment(True, camera, engine, names, 0.05, batch_frames=batch, mode="contours")
-        dt = time.perf_counter() - t0
+        rates.append(n / (time.perf_counter() - t0))
     objects = len(srv.segmented_objects)
     srv.segmented_objects.clear()
-    return {"value": n_frames / dt, "unit": "frames/s", "frames": n_frames, "batch_frames": batch, "mode": "contours",
+    return {"value": float(np.median(rates[1:])), "unit": "frames/s", "passes_frames_per_s": rates[1:], "frames": n_frames,
+            "batch_frames": batch, "mode": "contours",
             "camera": "%dx%d BGR u8, 8 distinct frames in pinned host memory" % (CAM_W, CAM_H), "objects_pushed": objects,
             "h2d_bytes_per_frame": CAM_H * CAM_W * 3,
             "api": "server.recognize_and_segment (drop-in for sem_seg_server.py:135-213), model stand-in of zero cost"}
