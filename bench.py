@@ -442,7 +442,7 @@ class FixedScores:
         return self.q[:x.shape[0]], 1.0 / 16, 128
 
 
-def reply_e2e(ssb200, torch, n_frames=2048, batch=64):
+def reply_e2e(ssb200, torch, n_frames=2048, batch=64, contour_stage=None):
     """Camera frames in pinned host memory -> recognize_and_segment(mode="contours") -> SegmentedObject
     protos in the deque: everything sem_seg_server.py:144-195 does per frame except the model, through
     the drop-in producer loop (H2D of every frame, K1, K2+K3, K4, K5, read-back of masks and region tables,
@@ -457,7 +457,8 @@ def reply_e2e(ssb200, torch, n_frames=2048, batch=64):
     for n in (4 * batch, n_frames, n_frames, n_frames):   # first pass: allocations, thread pools, lazy module loads
         camera = srv.ArrayCamera([cam[i % 8] for i in range(n)])
         t0 = time.perf_counter()
-        srv.recognize_and_segment(True, camera, engine, names, 0.05, batch_frames=batch, mode="contours")
+        srv.recognize_and_segment(True, camera, engine, names, 0.05, batch_frames=batch, mode="contours",
+                                  contour_workers=contour_stage)
         rates.append(n / (time.perf_counter() - t0))
     objects = len(srv.segmented_objects)
     srv.segmented_objects.clear()
@@ -711,6 +712,10 @@ def run_ssb(args):
     if rank == 0:
         # reply level: camera frames -> protos through the drop-in producer loop (the other ranks are idle)
         reply = reply_e2e(ssb200, torch)
+        gpu_stage = reply_e2e(ssb200, torch, contour_stage="gpu")
+        reply["contour_stage"] = "border following on host threads (ssb_contours_host, the default)"
+        reply["with_contour_integrals_on_the_gpu"] = {"value": gpu_stage["value"], "passes_frames_per_s": gpu_stage["passes_frames_per_s"],
+                                                      "objects_pushed": gpu_stage["objects_pushed"]}
         peak, peak_src = measured_peak()
         frames = world * BATCH * args.steps
         fps = frames / (dev_ms * 1e-3)

@@ -198,6 +198,17 @@ SSB_API int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, int 
                         int C, int max_regions, void *scratch, int32_t *count, int32_t *first, int32_t *parent,
                         int32_t *flags, uint32_t *hist, uint32_t *ring, void *stream);
 
+/* Replaces cv2.contourArea (sem_seg_server.py:93) and cv2.moments (:115) for the contours of the regions in a
+ * table written by ssb_blob_regions_u8: for every row, the closed-polygon sums over the border OpenCV follows
+ * (outer border of a foreground region; hole border of a background region that does not touch the ROI border),
+ *   moments [B][max_regions][3] i64 = a00, a10, a01:  contourArea = |a00| / 2,  m00 = a00 / 2,  m10 = a10 / 6,
+ *   m01 = a01 / 6 (sign of a00 folded in, as OpenCV does) -- exact integers, so the doubles formed from them equal
+ *   OpenCV's.  Rows of the outside background and rows at or beyond count[b] (or beyond max_regions) are zero /
+ *   not written.  `mask` is the array the table was made from; same ROI.  One thread per row walks the border. */
+SSB_API int ssb_contour_moments_u8(const uint8_t *mask, int B, int H, int W, int roi_h, int roi_w, int max_regions,
+                                   const int32_t *count, const int32_t *first, const int32_t *flags, int64_t *moments,
+                                   void *stream);
+
 /* Host-buffer convenience for callers that hold frames/logits in host memory (the reference's
  * situation: cap.read() and engine.run_inference both return host arrays).
  *
@@ -275,6 +286,15 @@ SSB_API int ssb_fold_regions_host(int B, int C, int max_regions, const int32_t *
 SSB_API int ssb_contours_host(const uint8_t *masks_host, int B, int H, int W, int roi_h, int roi_w, double min_area,
                               int max_candidates, int32_t *n_candidates, int32_t *cand_i32, double *cand_area,
                               int32_t *n_contours, int threads);
+
+/* ssb_candidates_from_moments_host: the list ssb_contours_host returns (same layout, same order), made from the
+ * region tables and the contour integrals of ssb_contour_moments_u8 (all copied to the host) instead of from the
+ * masks.  A frame whose table is incomplete, or in which one region has two candidate holes (their order depends on
+ * marks only the border following with marks has), gets n_candidates = -1: run ssb_contours_host on it. */
+SSB_API int ssb_candidates_from_moments_host(int B, int max_regions, int roi_w, const int32_t *count, const int32_t *first,
+                                             const int32_t *parent, const int32_t *flags, const int64_t *moments,
+                                             double min_area, int max_candidates, int32_t *n_candidates, int32_t *cand_i32,
+                                             double *cand_area, int threads);
 
 #ifdef __cplusplus
 }

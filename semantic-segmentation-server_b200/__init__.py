@@ -3,7 +3,8 @@ map, per-label segment statistics.  Host code in Python, kernels in libssb200.so
 sm_100a).  Importing this package loads the library and fails if it is not built."""
 from . import _cabi, contour_pool, hotpath, scheduler  # noqa: F401
 from .hotpath import (Centroid, FrameGeometry, HostPipeline, HostStaging, IngestPipeline, SegmentContour, argmax_stats,  # noqa: F401
-                      argmax_stats_nchw, blob_regions, contour_candidates_batch, fold_region_histograms, fold_regions_batch, frames_to_device,
+                      argmax_stats_nchw, blob_regions, candidates_from_moments_batch, contour_candidates_batch, contour_moments,
+                      fold_region_histograms, fold_regions_batch, frames_to_device,
                       objects_from_regions,
                       create_pascal_label_colormap, foreground_label_set, foreground_mask, load_labels,
                       nearest_index_table, normalise, objects_from_contours, objects_from_stats,

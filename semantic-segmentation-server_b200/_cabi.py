@@ -41,6 +41,10 @@ SIGNATURES = {
                                        _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_int]),
     "ssb_contours_host": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, ctypes.c_double, _c_int, _c_void_p,
                                    _c_void_p, _c_void_p, _c_void_p, _c_int]),
+    "ssb_contour_moments_u8": (_c_int, [_c_void_p, _c_int, _c_int, _c_int, _c_int, _c_int, _c_int, _c_void_p, _c_void_p,
+                                        _c_void_p, _c_void_p, _c_void_p]),
+    "ssb_candidates_from_moments_host": (_c_int, [_c_int, _c_int, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_void_p, _c_void_p,
+                                                  ctypes.c_double, _c_int, _c_void_p, _c_void_p, _c_void_p, _c_int]),
     "ssb_pipeline_create": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),
     "ssb_pipeline_destroy": (_c_int, [_c_void_p]),
     "ssb_pipeline_create_ingest": (_c_int, [ctypes.POINTER(_c_void_p), _c_int, _c_int, _c_int, _c_int, _c_int, _c_int]),

@@ -379,3 +379,101 @@ extern "C" int ssb_contours_host(const uint8_t *masks_host, int B, int H, int W,
     });
     return SSB_OK;
 }
+
+// Contour candidates of a batch from the region tables and the GPU's contour integrals (ssb_contour_moments_u8),
+// without touching a mask: the list ssb_contours_host returns, in the same order.
+//   * area / centroid: from the exact sums, with OpenCV's constants;
+//   * order: OpenCV lists contours in pre-order of the border tree, siblings in reverse order of discovery.  The tree is
+//     the enclosure tree of the table (outside background regions are transparent: what they hold is top level).  An
+//     outer border is discovered at its region's first pixel.  A hole border is discovered at the pixel left of the
+//     hole's first pixel UNLESS an earlier border left that pixel marked -- which can only change the order among the
+//     holes of one region, and only matters if two of them are candidates: such a frame is reported with
+//     n_candidates = -1 and goes through ssb_contours_host (so does a frame whose table is incomplete).
+extern "C" int ssb_candidates_from_moments_host(int B, int max_regions, int roi_w, const int32_t *count, const int32_t *first,
+                                                const int32_t *parent, const int32_t *flags, const int64_t *moments,
+                                                double min_area, int max_candidates, int32_t *n_candidates,
+                                                int32_t *cand_i32, double *cand_area, int threads) {
+    using namespace ssb;
+    if (B < 0 || max_regions < 1 || roi_w < 1 || max_candidates < 1) return fail(SSB_ERR_BAD_SHAPE, "bad shape");
+    if (B == 0) return SSB_OK;
+    if (!count || !first || !parent || !flags || !moments || !n_candidates || !cand_i32 || !cand_area)
+        return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
+    const size_t R = static_cast<size_t>(max_regions);
+    pool().run(B, threads, [&](int b) {
+        const int n = count[b];
+        if (n < 0 || n > max_regions) { n_candidates[b] = -1; return; }
+        const int32_t *f = first + R * b, *par = parent + R * b, *fl = flags + R * b;
+        const int64_t *mom = moments + R * 3 * b;
+        thread_local std::vector<int> ord, node_parent, kids, kid_begin, stack;
+        thread_local std::vector<char> cand;
+        ord.resize(n);
+        for (int i = 0; i < n; ++i) ord[i] = i;
+        std::sort(ord.begin(), ord.end(), [&](int a, int c) { return f[a] < f[c]; });
+        auto row_of = [&](int key) -> int {
+            auto pos = std::lower_bound(ord.begin(), ord.end(), key, [&](int a, int k) { return f[a] < k; });
+            return pos != ord.end() && f[*pos] == key ? *pos : -1;
+        };
+        auto outside = [&](int i) { return (fl[i] & 3) == 2; };
+        auto is_hole = [&](int i) { return (fl[i] & 3) == 0; };
+        auto area_of = [&](int i) { const double a = static_cast<double>(mom[3 * i]); return (a < 0 ? -a : a) * 0.5; };
+        auto disc_key = [&](int i) { return is_hole(i) ? f[i] - 1 : f[i]; };     // where the raster scan meets the border
+        // candidates (sem_seg_server.py:94, :117)
+        cand.assign(n, 0);
+        int n_cand = 0;
+        for (int i = 0; i < n; ++i)
+            if (!outside(i) && mom[3 * i] != 0 && area_of(i) >= min_area) { cand[i] = 1; ++n_cand; }
+        if (n_cand == 0) { n_candidates[b] = 0; return; }
+        // the border tree: parent node = enclosing region unless that is the outside (-1: top level)
+        node_parent.assign(n, -1);
+        for (int i = 0; i < n; ++i) {
+            if (outside(i) || par[i] < 0) continue;
+            const int j = row_of(par[i]);
+            node_parent[i] = (j < 0 || outside(j)) ? -1 : j;
+        }
+        if (n_cand > 1) {      // two candidate holes of one region: their order depends on marks this path does not have
+            for (int i = 0; i < n; ++i) {
+                if (!cand[i] || !is_hole(i)) continue;
+                for (int k = i + 1; k < n; ++k)
+                    if (cand[k] && is_hole(k) && node_parent[k] == node_parent[i]) { n_candidates[b] = -1; return; }
+            }
+        }
+        // children of every node (and of the top level, index n), newest (largest discovery key) first
+        kids.clear();
+        for (int i = 0; i < n; ++i)
+            if (!outside(i)) kids.push_back(i);
+        auto pkey = [&](int i) { return node_parent[i] < 0 ? n : node_parent[i]; };
+        std::sort(kids.begin(), kids.end(), [&](int a, int c) {
+            return pkey(a) != pkey(c) ? pkey(a) < pkey(c) : disc_key(a) > disc_key(c);
+        });
+        kid_begin.assign(n + 2, 0);
+        for (int i : kids) ++kid_begin[pkey(i) + 1];
+        for (int i = 0; i <= n; ++i) kid_begin[i + 1] += kid_begin[i];
+        // pre-order
+        int out_n = 0;
+        stack.clear();
+        for (int k = kid_begin[n + 1] - 1; k >= kid_begin[n]; --k) stack.push_back(kids[k]);
+        while (!stack.empty()) {
+            const int i = stack.back();
+            stack.pop_back();
+            if (cand[i]) {
+                if (out_n < max_candidates) {
+                    const long long a00i = mom[3 * i];
+                    const double a00 = static_cast<double>(a00i);
+                    const double db1_2 = a00i > 0 ? 0.5 : -0.5;
+                    const double db1_6 = a00i > 0 ? 0.16666666666666666666666666666667 : -0.16666666666666666666666666666667;
+                    const double m00 = a00 * db1_2, m10 = static_cast<double>(mom[3 * i + 1]) * db1_6,
+                                 m01 = static_cast<double>(mom[3 * i + 2]) * db1_6;
+                    int32_t *o = cand_i32 + (static_cast<size_t>(b) * max_candidates + out_n) * 4;
+                    o[0] = is_hole(i); o[1] = f[i];
+                    o[2] = static_cast<int32_t>(m10 / m00);
+                    o[3] = static_cast<int32_t>(m01 / m00);
+                    cand_area[static_cast<size_t>(b) * max_candidates + out_n] = area_of(i);
+                }
+                ++out_n;
+            }
+            for (int k = kid_begin[i + 1] - 1; k >= kid_begin[i]; --k) stack.push_back(kids[k]);
+        }
+        n_candidates[b] = out_n;
+    });
+    return SSB_OK;
+}

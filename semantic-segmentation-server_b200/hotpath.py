@@ -420,6 +420,52 @@ def contour_candidates_batch(masks_host, roi_h, roi_w, min_area, threads=8, max_
     return out
 
 
+def contour_moments(masks, tables, roi_h, roi_w, stream=None):
+    """Contour integrals (contourArea / moments as exact integers, C-ABI: ssb_contour_moments_u8) of every region in
+    `tables` (what blob_regions returned for these masks): adds tables["moments"], [B,R,3] int64, and returns it."""
+    _require_cuda(masks, "masks")
+    b, h, w = masks.shape
+    r = tables["first"].shape[1]
+    mom = tables.get("moments")
+    if mom is None or mom.shape != (b, r, 3) or mom.device != masks.device:
+        mom = torch.empty((b, r, 3), dtype=torch.int64, device=masks.device)
+        tables["moments"] = mom
+    with torch.cuda.device(masks.device):
+        _cabi.check(_cabi.lib.ssb_contour_moments_u8(masks.data_ptr(), b, h, w, roi_h, roi_w, r, tables["count"].data_ptr(),
+                                                     tables["first"].data_ptr(), tables["flags"].data_ptr(), mom.data_ptr(),
+                                                     _stream_ptr(stream)))
+    return mom
+
+
+def candidates_from_moments_batch(tables_host, roi_w, min_area, threads=8, max_candidates=64, scratch=None):
+    """contour_candidates_batch without the masks: the same per-frame candidate lists, in OpenCV's contour order, from
+    the region tables and their contour integrals (host numpy arrays; C-ABI: ssb_candidates_from_moments_host).
+    None for a frame that needs the masks after all (incomplete table, two candidate holes in one region, more than
+    `max_candidates` candidates)."""
+    count, first, parent, flags = (np.ascontiguousarray(tables_host[k]) for k in ("count", "first", "parent", "flags"))
+    mom = np.ascontiguousarray(tables_host["moments"])
+    b, r = first.shape
+    scratch = {} if scratch is None else scratch
+    if scratch.get("cand_shape") != (b, max_candidates):
+        scratch.update(cand_shape=(b, max_candidates), n=np.empty((b,), np.int32), ci=np.empty((b, max_candidates, 4), np.int32),
+                       ca=np.empty((b, max_candidates), np.float64))
+    n, ci, ca = scratch["n"], scratch["ci"], scratch["ca"]
+    _cabi.check(_cabi.lib.ssb_candidates_from_moments_host(b, r, roi_w, count.ctypes.data, first.ctypes.data, parent.ctypes.data,
+                                                           flags.ctypes.data, mom.ctypes.data, float(min_area), max_candidates,
+                                                           n.ctypes.data, ci.ctypes.data, ca.ctypes.data, threads))
+    out = []
+    for i in range(b):
+        k = int(n[i])
+        if k < 0 or k > max_candidates:
+            out.append(None)
+        elif k == 0:
+            out.append([])
+        else:
+            rows, areas = ci[i, :k].tolist(), ca[i, :k].tolist()
+            out.append([(rw[0], rw[1], a, rw[2], rw[3]) for rw, a in zip(rows, areas)])
+    return out
+
+
 def frames_to_device(frames, dst, staging=None, threads=8, stream=None):
     """The frames cap.read() returned (a list of equally shaped C-contiguous uint8 arrays) -> dst[:len(frames)]
     (device tensor [B,Hc,Wc,3]) on `stream` (C-ABI: ssb_frames_to_device).  Frames in page-locked memory are

@@ -153,7 +153,7 @@ def _open_camera(camera_idx):
     return cv2.VideoCapture(camera_idx)
 
 
-def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, mode, dev, out_q, stop):
+def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, mode, dev, out_q, stop, gpu_contours=False):
     """Feeder thread of recognize_and_segment: reads frames, gathers them into one of two pinned buffers,
     and enqueues transfer + K1 + model + K2/K3 (+ K4/K5) on its own CUDA stream.  Each batch goes to the
     consumer as (n_frames, geometry, device results, CUDA event); None ends the stream, an exception is
@@ -213,6 +213,8 @@ def _feed_batches(cap, engine, keep_aspect_ratio, width, height, batch_frames, m
                     # the table tensors rotate over four sets: one being filled, one queued, one being read back
                     tables[k % 4] = hotpath.blob_regions(masks, label_maps, geom.roi_h, geom.roi_w,
                                                          logits.shape[1 if nchw else 3], REGION_ROWS, out=tables[k % 4])
+                    if gpu_contours:
+                        hotpath.contour_moments(masks, tables[k % 4], geom.roi_h, geom.roi_w)   # :93, :115 as exact integers
                     res["tables"] = dict(tables[k % 4], mask=masks)
                 done = torch.cuda.Event()
                 done.record(stream)
@@ -233,7 +235,9 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
     thread reads back batch n, runs the OpenCV tails and pushes the objects -- in frame order, so the deque
     looks exactly as the reference's.  `contour_workers`: where the contour stage (sem_seg_server.py:88-122)
     runs -- None: the library's own border following on host threads (same contours and numbers as OpenCV);
-    k > 0: cv2 in k worker processes; 0: cv2 in this process."""
+    "gpu": contour integrals on the GPU with the region tables (masks stay on the device; the rare frame whose contour
+    order cannot be told from the tables falls back to the host border following); k > 0: cv2 in k worker processes;
+    0: cv2 in this process."""
     import queue
     import threading
     segmented_objects.clear()
@@ -246,7 +250,8 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
     fold_scratch = {}
     batches, stop = queue.Queue(maxsize=1), threading.Event()
     feeder = threading.Thread(target=_feed_batches, daemon=True,
-                              args=(cap, engine, keep_aspect_ratio, width, height, batch_frames, mode, dev, batches, stop))
+                              args=(cap, engine, keep_aspect_ratio, width, height, batch_frames, mode, dev, batches, stop,
+                                    contour_workers == "gpu"))
     feeder.start()
     copy_stream = torch.cuda.Stream(dev)
     try:
@@ -257,7 +262,8 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
             if isinstance(item, BaseException):
                 raise item
             n_frames, geom, res, ready = item
-            workers = _contour_workers(contour_workers, batch_frames * height * width) if mode == "contours" and contour_workers else None
+            workers = (_contour_workers(contour_workers, batch_frames * height * width)
+                       if mode == "contours" and isinstance(contour_workers, int) and contour_workers > 0 else None)
             with torch.cuda.stream(copy_stream):
                 copy_stream.wait_event(ready)
                 if mode == "contours" and workers is not None:
@@ -267,12 +273,33 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
                     masks_sh.copy_(res["tables"]["mask"][:n_frames], non_blocking=True)
                     tables_h = staging.fetch({k: v for k, v in res["tables"].items() if k != "mask"})   # one wait for all
                     tables_h["mask"] = masks_sh.numpy()
+                elif mode == "contours" and contour_workers == "gpu":
+                    # the contour integrals came from the GPU with the tables: the masks stay on the device
+                    tables_h = staging.fetch({k: v for k, v in res["tables"].items() if k != "mask"})
                 elif mode == "contours":
                     tables_h = staging.fetch(res["tables"])                       # pinned buffers, one wait
                 else:
                     stats_h = staging.fetch({"stats": res["stats"]})["stats"]
             n_batches += 1
-            if mode == "contours":
+            if mode == "contours" and contour_workers == "gpu":
+                enclosed = hotpath.fold_regions_batch(tables_h, HOST_THREADS, fold_scratch)
+                candidates = hotpath.candidates_from_moments_batch(tables_h, geom.roi_w, segment_centroid_min_area, HOST_THREADS,
+                                                                   scratch=fold_scratch)
+                per_frame = []
+                for i in range(n_frames):
+                    objs = None if candidates[i] is None else contour_pool.objects_from_candidates(candidates[i], enclosed[i], labels)
+                    if objs is None:
+                        # incomplete table, or the order of two candidate holes of one region is at stake: this frame's
+                        # mask comes to the host after all and goes through the border following with marks
+                        mask_i = res["tables"]["mask"][i:i + 1].cpu().numpy()
+                        cand = hotpath.contour_candidates_batch(mask_i, geom.roi_h, geom.roi_w, segment_centroid_min_area, 1)[0]
+                        objs = None if cand is None else contour_pool.objects_from_candidates(cand, enclosed[i], labels)
+                    if objs is None:
+                        objs = hotpath.objects_from_regions(
+                            res["tables"]["mask"][i, :geom.roi_h, :geom.roi_w].cpu().numpy(), enclosed[i], segment_centroid_min_area,
+                            labels, label_map=lambda: res["label_maps"][i, :geom.roi_h, :geom.roi_w].cpu().numpy())
+                    per_frame.append(objs)
+            elif mode == "contours":
                 masks_h = tables_h["mask"][:, :geom.roi_h, :geom.roi_w]
                 label_maps = res["label_maps"]
                 if workers is not None:

@@ -156,3 +156,126 @@ def test_native_contour_stage_equals_opencv_on_ten_thousand_masks():
     # a cut-short candidate list is reported, not silently truncated
     noisy = _random_masks(rng, 2, H, W, 0)
     assert ssb200.contour_candidates_batch(noisy, H, W, 0.0, max_candidates=3) == [None, None]
+
+
+def _row_moments(mask, first, flags):
+    """CPU twin of ssb_contour_moments_u8 for one frame (plain Python): the closed-polygon sums over the border the
+    kernel walks for every table row."""
+    h, w = mask.shape
+    dx, dy = [1, 1, 0, -1, -1, -1, 0, 1], [0, -1, -1, -1, 0, 1, 1, 1]
+
+    def fg(x, y):
+        return 0 <= x < w and 0 <= y < h and mask[y, x] != 0
+    out = np.zeros((len(first), 3), np.int64)
+    for r, (fp, fl) in enumerate(zip(first.tolist(), (flags & 3).tolist())):
+        if fl == 2:
+            continue
+        hole = fl == 0
+        y0, x0 = divmod(fp, w)
+        x0 -= 1 if hole else 0
+        s_end = s = 0 if hole else 4
+        while True:
+            s = (s - 1) & 7
+            if fg(x0 + dx[s], y0 + dy[s]) or s == s_end:
+                break
+        if not fg(x0 + dx[s], y0 + dy[s]):
+            continue
+        x1, y1, x, y, pts = x0 + dx[s], y0 + dy[s], x0, y0, []
+        while True:
+            while True:
+                s += 1
+                nx, ny = x + dx[s & 7], y + dy[s & 7]
+                if fg(nx, ny):
+                    break
+            s &= 7
+            pts.append((x, y))
+            if (nx, ny) == (x0, y0) and (x, y) == (x1, y1):
+                break
+            x, y, s = nx, ny, (s + 4) & 7
+        px, py = pts[-1]
+        for x, y in pts:
+            d = px * y - x * py
+            out[r] += (d, d * (px + x), d * (py + y))
+            px, py = x, y
+    return out
+
+
+def test_candidates_from_tables_and_moments_equal_the_border_following():
+    """Region tables + contour integrals -> the candidate list (order, flags, keys, areas, centroids) the border
+    following with marks gives on the mask; frames where two holes of one region are candidates ask for the masks."""
+    import ssb200
+    from oracle import segpath as sp
+    rng = np.random.default_rng(31)
+    H, W, R = 40, 56, 1024
+    checked = asked = 0
+    for rep in range(12):
+        masks = _random_masks(rng, 16, H, W, rep)
+        if rep == 0:                                   # a ring with two big holes separated by a wall, and an island
+            masks[0] = 0
+            masks[0, 3:37, 4:52] = 255
+            masks[0, 8:30, 8:25] = 0
+            masks[0, 8:30, 27:48] = 0
+            masks[0, 12:20, 30:40] = 255
+        labs = np.zeros_like(masks)
+        count = np.zeros(16, np.int32)
+        first, parent, flags = (np.zeros((16, R), np.int32) for _ in range(3))
+        mom = np.zeros((16, R, 3), np.int64)
+        for i in range(16):
+            n, f, p, fl, _, _ = scipy_table(masks[i], labs[i])
+            perm = rng.permutation(n)
+            count[i] = n
+            first[i, :n], parent[i, :n], flags[i, :n] = f[perm], p[perm], fl[perm]
+            mom[i, :n] = _row_moments(masks[i], f[perm], fl[perm])
+        tables = {"count": count, "first": first, "parent": parent, "flags": flags, "moments": mom}
+        for min_area in (0.5, 30.0, 150.0):
+            got = ssb200.candidates_from_moments_batch(tables, W, min_area, threads=3, max_candidates=1024)
+            want = ssb200.contour_candidates_batch(masks, H, W, min_area, threads=3, max_candidates=1024)
+            for i in range(16):
+                if got[i] is None:
+                    holes = [c for c in want[i] if c[0]]
+                    assert len(holes) >= 2, (rep, i)       # only ever asked for where hole order is at stake
+                    asked += 1
+                else:
+                    assert got[i] == want[i], (rep, i, min_area)
+                    checked += 1
+    assert checked > 300 and asked >= 1, (checked, asked)
+
+
+@pytest.mark.gpu
+def test_gpu_contour_moments_give_the_border_following_candidates():
+    """Mask kernel -> region tables -> contour integrals on the GPU -> candidates, against the border following with
+    marks on the same masks (which equals OpenCV): every frame that does not ask for the masks must agree exactly."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    from oracle import segpath as sp
+    rng = np.random.default_rng(77)
+    checked = asked = 0
+    for (B, H, W, roi_h, roi_w) in ((24, 96, 130, 96, 130), (16, 513, 513, 288, 513), (12, 64, 80, 50, 77)):
+        labs = np.zeros((B, H, W), np.uint8)
+        for i in range(B):
+            if i % 3 == 2:
+                labs[i] = np.pad(sp.blobby_label_map(i, roi_h, roi_w), ((0, H - roi_h), (0, W - roi_w)))
+            else:
+                m, l = random_label_map(rng, i)
+                reps = (-(-H // l.shape[0]), -(-W // l.shape[1]))
+                labs[i] = np.tile(l, reps)[:H, :W]
+        lab_d = torch.from_numpy(labs).cuda()
+        mask_d = ssb200.foreground_mask(lab_d, roi_h, roi_w)
+        t = ssb200.blob_regions(mask_d, lab_d, roi_h, roi_w, 21, 4096)
+        ssb200.contour_moments(mask_d, t, roi_h, roi_w)
+        torch.cuda.synchronize()
+        th = {k: v.cpu().numpy() for k, v in t.items()}
+        masks = mask_d.cpu().numpy()
+        for min_area in (0.5, 40.0, 0.05 * 513 * 513):
+            got = ssb200.candidates_from_moments_batch(th, roi_w, min_area, threads=4, max_candidates=4096)
+            want = ssb200.contour_candidates_batch(masks, roi_h, roi_w, min_area, threads=4, max_candidates=4096)
+            for i in range(B):
+                if got[i] is None:
+                    assert th["count"][i] > 4096 or len([c for c in want[i] if c[0]]) >= 2, (B, i)
+                    asked += 1
+                else:
+                    assert got[i] == want[i], (B, H, W, i, min_area)
+                    checked += 1
+    assert checked > 100

@@ -101,9 +101,12 @@ class _MapEngine:
 
 
 @pytest.mark.gpu
-def test_recognize_and_segment_reproduces_reference_replies(srv, golden):
+@pytest.mark.parametrize("contour_stage", [None, "gpu", 2, 0])
+def test_recognize_and_segment_reproduces_reference_replies(srv, golden, contour_stage):
     """Whole producer loop (camera frame -> K1 -> model stand-in -> K2/K3 -> mask -> contours ->
-    normalised protos in the deque) against what the reference's own loop left in ITS deque."""
+    normalised protos in the deque) against what the reference's own loop left in ITS deque -- with every
+    implementation of the contour stage: the library's border following on host threads (default), contour
+    integrals on the GPU, cv2 in worker processes, cv2 in this process."""
     import torch
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
@@ -116,7 +119,8 @@ def test_recognize_and_segment_reproduces_reference_replies(srv, golden):
         frames = [np.zeros((ch, cw, 3), np.uint8)] * 3                     # a batch of 3 identical frames
         engine = _MapEngine(H, W, [g[name + "_label_map"]] * 3)
         srv.recognize_and_segment(True, srv.ArrayCamera(frames), engine, names,
-                                  float(g[name + "_min_area_ratio"]), batch_frames=2, mode="contours")
+                                  float(g[name + "_min_area_ratio"]), batch_frames=2, mode="contours",
+                                  contour_workers=contour_stage)
         got = list(srv.segmented_objects)
         want_names, want_vals = g[name + "_obj_names"].tolist(), g[name + "_obj_vals"]
         assert len(got) == 3 * len(want_names), name
