@@ -42,7 +42,10 @@ def main():
     blobby = field.repeat_interleave(16, 1).repeat_interleave(16, 2)[:, :H, :W].to(torch.uint8).contiguous()
     bmask = ssb200.foreground_mask(blobby, geom.roi_h, geom.roi_w, cm)
     for _ in range(REPS):
-        ssb200.blob_regions(bmask, blobby, geom.roi_h, geom.roi_w, 21, 1024)
+        tabs = ssb200.blob_regions(bmask, blobby, geom.roi_h, geom.roi_w, 21, 1024)
+    # K6 on those tables
+    for _ in range(REPS):
+        ssb200.contour_moments(bmask, tabs, geom.roi_h, geom.roi_w)
     del q
     # K2+K3 fp16, Cityscapes shape
     h16 = torch.randn((8, 1024, 2048, 19), dtype=torch.float16, device="cuda", generator=g)
