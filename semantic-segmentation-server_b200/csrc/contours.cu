@@ -14,16 +14,22 @@
 // A warp per table row; the walk is serial, rows and frames are parallel.
 // The host restatement with marks (csrc/hostpath.cu, ssb_contours_host) is the reference these sums are tested
 // against, and the fallback where the ORDER of sibling hole contours matters (see hotpath.candidates_from_moments).
+#include <cstdlib>
+
 #include "ssb_common.cuh"
 
 namespace ssb {
 namespace {
+
+constexpr long long kMomentsUnknown = static_cast<long long>(0x8000000000000000ull);   // a10 of a row whose border was not walked to the end
+constexpr int kDefaultMaxSteps = 32768;
 
 struct MomentParams {
     const uint8_t *mask;      // [B][H][W]
     int B, H, W, roi_h, roi_w, max_regions;
     const int *count, *first, *flags;
     long long *moments;       // [B][max_regions][3]
+    int max_steps;            // a border longer than this is left to the host (row marked "unknown")
 };
 
 // A warp per table row: eight lanes look at the eight neighbours of the current border pixel at once (one load
@@ -36,6 +42,7 @@ __global__ void __launch_bounds__(128) contour_moments_kernel(const MomentParams
     const long long tab = static_cast<long long>(f) * p.max_regions + row;
     const int fl = p.flags[tab] & 3;
     long long a00 = 0, a10 = 0, a01 = 0;
+    bool unknown = false;
     if (fl != 2) {                                       // not the outside
         const bool is_hole = fl == 0;
         const int fp = p.first[tab];
@@ -60,7 +67,7 @@ __global__ void __launch_bounds__(128) contour_moments_kernel(const MomentParams
                 s = (s - 1) & 7;
             } while (!((nb >> s) & 1u));
             const int x1 = x0 + step_x(s), y1 = y0 + step_y(s);
-            int x = x0, y = y0, px = x0, py = y0;
+            int x = x0, y = y0, px = x0, py = y0, steps = 0;
             bool first = true;
             for (;;) {
                 // first foreground neighbour counter-clockwise from direction s + 1
@@ -75,6 +82,7 @@ __global__ void __launch_bounds__(128) contour_moments_kernel(const MomentParams
                 first = false;
                 px = x; py = y;
                 if (nx == x0 && ny == y0 && x == x1 && y == y1) break;
+                if (++steps > p.max_steps) { unknown = true; break; }       // bounded GPU time: the host walks this one
                 x = nx; y = ny;
                 s = (s + 4) & 7;
                 nb = neighbours(x, y);
@@ -83,6 +91,7 @@ __global__ void __launch_bounds__(128) contour_moments_kernel(const MomentParams
             a00 += d; a10 += d * (px + x0); a01 += d * (py + y0);
         }
     }
+    if (unknown) { a00 = 0; a10 = kMomentsUnknown; a01 = 0; }
     if (lane == 0) {
         p.moments[tab * 3 + 0] = a00;
         p.moments[tab * 3 + 1] = a10;
@@ -102,7 +111,9 @@ extern "C" int ssb_contour_moments_u8(const uint8_t *mask, int B, int H, int W, 
     if (B == 0) return SSB_OK;
     if (B > 65535) return fail(SSB_ERR_LIMIT, "B must be <= 65535");
     if (!mask || !count || !first || !flags || !moments) return fail(SSB_ERR_BAD_POINTER, "NULL buffer");
-    MomentParams p{mask, B, H, W, roi_h, roi_w, max_regions, count, first, flags, reinterpret_cast<long long *>(moments)};
+    int max_steps = kDefaultMaxSteps;
+    if (const char *env = getenv("SSB_MOMENTS_MAX_STEPS")) max_steps = atoi(env) > 0 ? atoi(env) : max_steps;   // test knob
+    MomentParams p{mask, B, H, W, roi_h, roi_w, max_regions, count, first, flags, reinterpret_cast<long long *>(moments), max_steps};
     const dim3 grid((max_regions + 3) / 4, B), block(128);   // a warp per row
     SSB_CUDA_TRY(launch_pdl(contour_moments_kernel, grid, block, 0, static_cast<cudaStream_t>(stream), p));
     return SSB_OK;

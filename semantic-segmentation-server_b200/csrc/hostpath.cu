@@ -417,6 +417,8 @@ extern "C" int ssb_candidates_from_moments_host(int B, int max_regions, int roi_
         auto is_hole = [&](int i) { return (fl[i] & 3) == 0; };
         auto area_of = [&](int i) { const double a = static_cast<double>(mom[3 * i]); return (a < 0 ? -a : a) * 0.5; };
         auto disc_key = [&](int i) { return is_hole(i) ? f[i] - 1 : f[i]; };     // where the raster scan meets the border
+        for (int i = 0; i < n; ++i)                       // a border the GPU gave up on (longer than its step limit)
+            if (mom[3 * i] == 0 && mom[3 * i + 1] == static_cast<int64_t>(0x8000000000000000ull)) { n_candidates[b] = -1; return; }
         // candidates (sem_seg_server.py:94, :117)
         cand.assign(n, 0);
         int n_cand = 0;

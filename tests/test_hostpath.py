@@ -279,3 +279,29 @@ def test_gpu_contour_moments_give_the_border_following_candidates():
                     assert got[i] == want[i], (B, H, W, i, min_area)
                     checked += 1
     assert checked > 100
+
+
+@pytest.mark.gpu
+def test_gpu_contour_moments_give_up_on_long_borders(monkeypatch):
+    """The walk on the GPU is bounded: a border longer than the step limit marks its row unknown and the frame asks for
+    the masks (here with the limit lowered to 40 steps, so that ordinary blobs hit it)."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    from oracle import segpath as sp
+    monkeypatch.setenv("SSB_MOMENTS_MAX_STEPS", "40")
+    labs = np.stack([np.pad(sp.blobby_label_map(s, 96, 130), ((0, 4), (0, 0))) for s in range(6)]).astype(np.uint8)
+    labs[5] = 0
+    labs[5, 10:14, 10:14] = 15                           # a border of 12 steps: within the limit
+    lab_d = torch.from_numpy(labs).cuda()
+    mask_d = ssb200.foreground_mask(lab_d, 96, 130)
+    t = ssb200.blob_regions(mask_d, lab_d, 96, 130, 21, 256)
+    ssb200.contour_moments(mask_d, t, 96, 130)
+    torch.cuda.synchronize()
+    th = {k: v.cpu().numpy() for k, v in t.items()}
+    got = ssb200.candidates_from_moments_batch(th, 130, 1.0, threads=2)
+    want = ssb200.contour_candidates_batch(mask_d.cpu().numpy(), 96, 130, 1.0, threads=2)
+    assert got[5] == want[5] and len(want[5]) == 1
+    assert sum(g is None for g in got[:5]) >= 3
+    assert all(g is None or g == w for g, w in zip(got, want))

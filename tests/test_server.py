@@ -101,8 +101,8 @@ class _MapEngine:
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("contour_stage", [None, "gpu", 2, 0])
-def test_recognize_and_segment_reproduces_reference_replies(srv, golden, contour_stage):
+@pytest.mark.parametrize("contour_stage", [None, "gpu", "gpu-short-walks", 2, 0])
+def test_recognize_and_segment_reproduces_reference_replies(srv, golden, contour_stage, monkeypatch):
     """Whole producer loop (camera frame -> K1 -> model stand-in -> K2/K3 -> mask -> contours ->
     normalised protos in the deque) against what the reference's own loop left in ITS deque -- with every
     implementation of the contour stage: the library's border following on host threads (default), contour
@@ -110,6 +110,9 @@ def test_recognize_and_segment_reproduces_reference_replies(srv, golden, contour
     import torch
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
+    if contour_stage == "gpu-short-walks":                 # every real border exceeds the limit: all frames fall back to the host
+        monkeypatch.setenv("SSB_MOMENTS_MAX_STEPS", "25")
+        contour_stage = "gpu"
     g = golden("objects.npz")
     lab = golden("labels_colormap.npz")
     names = dict(zip(lab["label_ids"].tolist(), lab["label_names"].tolist()))
