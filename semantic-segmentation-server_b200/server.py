@@ -415,6 +415,9 @@ def build_arg_parser():
     parser.add_argument("--mode", choices=["contours", "labels"], default="contours", help="object definition (new)")
     parser.add_argument("--engine", choices=["synthetic", "torchvision", "torchvision-fp16"], default="synthetic",
                         help="class-score provider standing in for the Edge TPU model (new)")
+    parser.add_argument("--contour_stage", choices=["host", "gpu", "cv2", "cv2-processes"], default="host",
+                        help="where findContours / contourArea / moments run: the library's border following on host threads, "
+                             "contour integrals on the GPU, OpenCV in this process, OpenCV in worker processes (new)")
     parser.add_argument("--port", default="[::]:50051")
     parser.set_defaults(keep_aspect_ratio=True)      # as the reference: always true (:246-259)
     return parser
@@ -431,8 +434,9 @@ def serve(argv=None):
     camera_res = int(cap.get(cv2.CAP_PROP_FRAME_WIDTH)), int(cap.get(cv2.CAP_PROP_FRAME_HEIGHT))
     cap.release()
     with concurrent.futures.ThreadPoolExecutor(max_workers=10) as executor:
+        stage = {"host": None, "gpu": "gpu", "cv2": 0, "cv2-processes": CONTOUR_WORKERS}[args.contour_stage]
         future = executor.submit(recognize_and_segment, args.keep_aspect_ratio, args.camera_idx, engine, labels,
-                                 args.min_area_ratio, args.batch_frames, args.mode)
+                                 args.min_area_ratio, args.batch_frames, args.mode, 0, None, stage)
         server = grpc.server(executor)
         add_SemanticSegmentationServicer_to_server(SemanticSegmentationServicer(args.num_detections, camera_res), server)
         server.add_insecure_port(args.port)
