@@ -86,8 +86,14 @@ class HostPool {
     unsigned generation_ = 0;
 };
 
+// Two pools: a pool runs one job at a time, and the feeder's frame gather (milliseconds per batch with pageable frames)
+// must not hold up the consumer's table fold / contour stage of the previous batch.
 HostPool &pool() {
     static HostPool *p = new HostPool();   // never destroyed: its detached workers may outlive static destruction
+    return *p;
+}
+HostPool &upload_pool() {
+    static HostPool *p = new HostPool();
     return *p;
 }
 
@@ -141,7 +147,7 @@ extern "C" int ssb_frames_to_device(const uint8_t *const *frames_host, int n, si
         std::vector<int> todo;
         for (int i = 0; i < n; ++i)
             if (!direct[i]) todo.push_back(i);
-        pool().run(static_cast<int>(todo.size()), threads, [&](int j) {
+        upload_pool().run(static_cast<int>(todo.size()), threads, [&](int j) {
             cudaSetDevice(dev);            // pool threads start on device 0
             send(todo[j]);
         });
