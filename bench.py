@@ -712,10 +712,10 @@ def run_ssb(args):
     if rank == 0:
         # reply level: camera frames -> protos through the drop-in producer loop (the other ranks are idle)
         reply = reply_e2e(ssb200, torch)
-        gpu_stage = reply_e2e(ssb200, torch, contour_stage="gpu")
-        reply["contour_stage"] = "border following on host threads (ssb_contours_host, the default)"
-        reply["with_contour_integrals_on_the_gpu"] = {"value": gpu_stage["value"], "passes_frames_per_s": gpu_stage["passes_frames_per_s"],
-                                                      "objects_pushed": gpu_stage["objects_pushed"]}
+        host_stage = reply_e2e(ssb200, torch, contour_stage="host")
+        reply["contour_stage"] = "contour integrals on the GPU (ssb_contour_moments_u8, the default)"
+        reply["with_border_following_on_host_threads"] = {"value": host_stage["value"], "passes_frames_per_s": host_stage["passes_frames_per_s"],
+                                                          "objects_pushed": host_stage["objects_pushed"]}
         peak, peak_src = measured_peak()
         frames = world * BATCH * args.steps
         fps = frames / (dev_ms * 1e-3)

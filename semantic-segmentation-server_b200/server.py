@@ -234,12 +234,14 @@ def recognize_and_segment(keep_aspect_ratio, camera_idx, engine, labels, min_are
     Two stages run side by side: a feeder thread gathers batch n+1 and enqueues its GPU work while this
     thread reads back batch n, runs the OpenCV tails and pushes the objects -- in frame order, so the deque
     looks exactly as the reference's.  `contour_workers`: where the contour stage (sem_seg_server.py:88-122)
-    runs -- None: the library's own border following on host threads (same contours and numbers as OpenCV);
-    "gpu": contour integrals on the GPU with the region tables (masks stay on the device; the rare frame whose contour
-    order cannot be told from the tables falls back to the host border following); k > 0: cv2 in k worker processes;
-    0: cv2 in this process."""
+    runs -- None or "gpu": contour integrals on the GPU with the region tables (masks stay on the device; the rare
+    frame whose contour order cannot be told from the tables, or whose border exceeds the walk limit, goes through the
+    host border following); "host": the library's own border following on host threads for every frame (same contours
+    and numbers as OpenCV); k > 0: cv2 in k worker processes; 0: cv2 in this process."""
     import queue
     import threading
+    if contour_workers is None:
+        contour_workers = "gpu"
     segmented_objects.clear()
     _, height, width, _ = engine.get_input_tensor_shape()
     segment_centroid_min_area = min_area_ratio * height * width
@@ -415,9 +417,9 @@ def build_arg_parser():
     parser.add_argument("--mode", choices=["contours", "labels"], default="contours", help="object definition (new)")
     parser.add_argument("--engine", choices=["synthetic", "torchvision", "torchvision-fp16"], default="synthetic",
                         help="class-score provider standing in for the Edge TPU model (new)")
-    parser.add_argument("--contour_stage", choices=["host", "gpu", "cv2", "cv2-processes"], default="host",
+    parser.add_argument("--contour_stage", choices=["gpu", "host", "cv2", "cv2-processes"], default="gpu",
                         help="where findContours / contourArea / moments run: the library's border following on host threads, "
-                             "contour integrals on the GPU, OpenCV in this process, OpenCV in worker processes (new)")
+                             "contour integrals on the GPU (default), OpenCV in this process, OpenCV in worker processes (new)")
     parser.add_argument("--port", default="[::]:50051")
     parser.set_defaults(keep_aspect_ratio=True)      # as the reference: always true (:246-259)
     return parser
@@ -434,7 +436,7 @@ def serve(argv=None):
     camera_res = int(cap.get(cv2.CAP_PROP_FRAME_WIDTH)), int(cap.get(cv2.CAP_PROP_FRAME_HEIGHT))
     cap.release()
     with concurrent.futures.ThreadPoolExecutor(max_workers=10) as executor:
-        stage = {"host": None, "gpu": "gpu", "cv2": 0, "cv2-processes": CONTOUR_WORKERS}[args.contour_stage]
+        stage = {"host": "host", "gpu": "gpu", "cv2": 0, "cv2-processes": CONTOUR_WORKERS}[args.contour_stage]
         future = executor.submit(recognize_and_segment, args.keep_aspect_ratio, args.camera_idx, engine, labels,
                                  args.min_area_ratio, args.batch_frames, args.mode, 0, None, stage)
         server = grpc.server(executor)

@@ -101,12 +101,13 @@ class _MapEngine:
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("contour_stage", [None, "gpu", "gpu-short-walks", 2, 0])
+@pytest.mark.parametrize("contour_stage", [None, "host", "gpu-short-walks", 2, 0])
 def test_recognize_and_segment_reproduces_reference_replies(srv, golden, contour_stage, monkeypatch):
     """Whole producer loop (camera frame -> K1 -> model stand-in -> K2/K3 -> mask -> contours ->
     normalised protos in the deque) against what the reference's own loop left in ITS deque -- with every
-    implementation of the contour stage: the library's border following on host threads (default), contour
-    integrals on the GPU, cv2 in worker processes, cv2 in this process."""
+    implementation of the contour stage: contour integrals on the GPU (default), the library's border following on
+    host threads, the GPU stage with a walk limit that sends every frame to the host, cv2 in worker processes, cv2
+    in this process."""
     import torch
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
