@@ -151,8 +151,9 @@ def run_reference(args):
     if rank != 0:
         return
     threads = cpu_threads()
-    batches = [synth_batch(1000 + i) for i in range(2)]
     from oracle import cport
+    # pages of the inputs spread over the memory nodes of the worker threads (not all on the generating thread's node)
+    batches = [cport.interleaved_copy(synth_batch(1000 + i), threads) for i in range(2)]
     out = _cpu_port_outputs()
     n_warm = 0
     for b in batches:
@@ -797,7 +798,8 @@ def main():
     if args.leg == "reference_literal":
         print(json.dumps(time_reference_literal()))
     elif args.leg == "cpu_port":
-        batches = [synth_batch(1000 + i) for i in range(2)]
+        from oracle import cport
+        batches = [cport.interleaved_copy(synth_batch(1000 + i), cpu_threads()) for i in range(2)]
         fps, passes, el = time_cpu_port(batches, cpu_threads(), min_seconds=10.0)
         t1 = time.perf_counter()
         from oracle import segpath as sp

@@ -56,6 +56,18 @@ def argmax_stats(logits, roi_h=None, roi_w=None, threads=1, want_labels=True, ou
     return labels, stats
 
 
+def interleaved_copy(a, threads):
+    """A copy of `a` whose pages were first touched by the pooled threads, 64 KB chunks handed out dynamically: spread
+    over the memory nodes the threads run on (what `numactl --interleave` does for a bandwidth-bound benchmark)."""
+    a = np.ascontiguousarray(a)
+    out = np.empty_like(a)
+    f = lib().oracle_interleaved_copy
+    f.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int]
+    if f(_p(out), _p(a), a.nbytes, threads) != 0:
+        raise RuntimeError("oracle_interleaved_copy failed")
+    return out
+
+
 def preprocess(frames_bgr, xtab, ytab, height, width, threads=1):
     """frames [B,Hc,Wc,3] u8 + NEAREST tables -> [B,H,W,3] u8 RGB, zero padded."""
     frames_bgr = np.ascontiguousarray(frames_bgr)
