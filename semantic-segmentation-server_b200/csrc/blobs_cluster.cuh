@@ -8,6 +8,10 @@ constexpr int kStrips = 8;            // CTAs per cluster = horizontal strips of
 #ifndef SSB_STRIP_TMA
 #define SSB_STRIP_TMA 1
 #endif
+#ifndef SSB_STRIP_WORD_FAST
+#define SSB_STRIP_WORD_FAST 1   // label counts: 0 = every word a lane per pixel; 1 = uniform words are counted by one lane each;
+                                // 2 = the same with the label bytes of the next 32 words requested one round ahead (slower)
+#endif
 #ifndef SSB_STRIP_STOP
 #define SSB_STRIP_STOP 0   // tuning: n > 0 ends the kernel after its n-th phase (cumulative phase timing)
 #endif
@@ -206,7 +210,7 @@ struct Strip {
 };
 
 #ifndef SSB_STRIP_MIN_CTAS
-#define SSB_STRIP_MIN_CTAS 1
+#define SSB_STRIP_MIN_CTAS 4   // 64 registers at 256 threads: 4 CTAs per SM, so 64 frames' clusters are resident at once
 #endif
 __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluster_kernel(const StripParams sp) {
     extern __shared__ __align__(16) unsigned char strip_smem[];
@@ -464,6 +468,49 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
             p.parent[tab + row] = x > 0 ? gfind(par, base + k.of_run(ly, x - 1)) : -1;
         }
     });
+    // The label counts below look at 32 words at a time, a lane per word, and need the words' label bytes (variant 2:
+    // those of a warp's first 32 words are requested here, so that they arrive while the cluster waits).
+    const int t_begin = static_cast<int>(static_cast<long long>(tasks) * warp / kStripWarps);
+    const int t_end = static_cast<int>(static_cast<long long>(tasks) * (warp + 1) / kStripWarps);
+    struct WordLook {
+        unsigned int v[9];      // the word's 32 label bytes as aligned 32-bit words
+        unsigned int off;       // byte phase of the first label in v[0]
+        unsigned int n_px;      // live pixels of the word; 0: not a candidate (several runs, ring work, past the range)
+        unsigned int starts;
+    };
+    // A word is a candidate for being counted whole if it lies inside one run and none of its pixels is foreground
+    // next to background (no ring work); whether its pixels carry one label is seen when the bytes are there.
+    auto look_ahead = [&](int t0) {
+        WordLook q;
+        q.n_px = 0u; q.off = 0u; q.starts = 0u;
+#pragma unroll
+        for (int j = 0; j < 9; ++j) q.v[j] = 0u;
+        const int tw = t0 + lane;
+        if (!SSB_STRIP_WORD_FAST || tw >= t_end) return q;
+        int ly, seg;
+        k.split(tw, ly, seg);
+        const SegBits b = seg_bits(k.bit_row(ly), seg, S, k.live_last);
+        q.starts = k.st[tw] & b.live;
+        bool cand = (q.starts & ~1u) == 0u;                              // one run from the first live pixel to the last
+        if (cand && p.ring && b.fg) {
+            const int gy = y0 + ly;
+            const unsigned int U = gy > 0 ? k.bit_row(ly - 1)[seg] : 0xffffffffu;
+            const unsigned int D = gy + 1 < p.roi_h ? k.bit_row(ly + 1)[seg] : 0xffffffffu;
+            cand = (b.fg & ((b.has_w & ~b.Wb) | (b.has_e & ~b.Eb) | ~U | ~D)) == 0u;
+        }
+        if (!cand) return q;
+        q.n_px = __popc(b.live);
+        // at least one byte of every 32-bit word loaded is a live pixel of this word
+        const uint8_t *src = lab_f + static_cast<long long>(y0 + ly) * p.W + seg * 32;
+        q.off = static_cast<unsigned int>(reinterpret_cast<uintptr_t>(src) & 3u);
+        const unsigned int *w32 = reinterpret_cast<const unsigned int *>(src - q.off);
+        const int n_bytes = static_cast<int>(q.off + q.n_px);
+#pragma unroll
+        for (int j = 0; j < 9; ++j)
+            if (4 * j < n_bytes) q.v[j] = w32[j];
+        return q;
+    };
+    WordLook look = look_ahead(SSB_STRIP_WORD_FAST == 2 ? t_begin : t_end);
     if (p.ring) cluster_barrier(); else __syncthreads();
     if (SSB_STRIP_STOP == 6) return;
 
@@ -490,10 +537,9 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
         const int row = slotp[id];
         return row < p.max_regions ? row : 0xFFFF;
     };
-    // ---- phase 8: label histograms, a lane per pixel.  A warp walks a contiguous range of words (no index
-    // ---- division per word) with the label bytes of the next three words already requested, and keeps the
-    // ---- count of ONE (row, label) pair in registers across its words: most words of a real mask are one
-    // ---- region with one label. ----
+    // ---- phase 8: label histograms.  A warp owns a contiguous range of words.  Words that are one run with one
+    // ---- label and no ring work are counted whole (a lane per WORD, see below); the others a lane per pixel,
+    // ---- with the count of ONE (row, label) pair kept in registers from word to word. ----
     {
         unsigned int cache_key = 0xffffffffu, cache_cnt = 0u;
         // n pixels of (row, label): into the CTA's shared-memory counts if the row has (or gets) a place there
@@ -511,22 +557,9 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
             if (cache_cnt && lane == 0) add_hist(cache_key >> 8, cache_key & 0xffu, cache_cnt);
             cache_cnt = 0u;
         };
-        int t = static_cast<int>(static_cast<long long>(tasks) * warp / kStripWarps);
-        const int t_end = static_cast<int>(static_cast<long long>(tasks) * (warp + 1) / kStripWarps);
-        int ly, seg;
-        k.split(t < tasks ? t : 0, ly, seg);
-        const int row_step = p.W - S * 32;                               // last word of a row -> first word of the next, minus 32
         const unsigned int below = 0xffffffffu >> (31 - lane);           // bits of lanes <= lane
-        // load cursor: runs three words ahead of the work cursor
-        const uint8_t *lp = lab_f + static_cast<long long>(y0 + ly) * p.W + seg * 32 + lane;
-        int l_t = t, l_seg = seg;
-        auto load_label = [&]() -> int {
-            const int v = (l_t < t_end && l_seg * 32 + lane < rw) ? *lp : 0;
-            ++l_t;
-            if (++l_seg == S) { l_seg = 0; lp += 32 + row_step; } else { lp += 32; }
-            return v;
-        };
-        auto step = [&](int lab) {
+        // one word, a lane per pixel
+        auto step = [&](int t, int ly, int seg, int lab) {
             const int x = seg * 32 + lane;
             unsigned int row = 0xFFFFu;
             if (x < rw) {
@@ -582,18 +615,89 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
                     }
                 }
             }
-            ++t;
-            if (++seg == S) { seg = 0; ++ly; }
         };
-        // three label registers, each reloaded right after its word is done and used again three words later
-        int la = load_label(), lb = load_label(), lc = load_label();
-        while (t < t_end) {
-            step(la); la = load_label();
-            if (t >= t_end) break;
-            step(lb); lb = load_label();
-            if (t >= t_end) break;
-            step(lc); lc = load_label();
+        auto label_of = [&](int ly, int seg) -> int {
+            const int x = seg * 32 + lane;
+            return x < rw ? lab_f[static_cast<long long>(y0 + ly) * p.W + x] : 0;
+        };
+#if SSB_STRIP_WORD_FAST
+        // 32 words at a time, first a LANE per word: a candidate word whose pixels all carry one label is counted by
+        // its lane alone -- words of the same (row, label) among the 32 by one lane for all.  The other words then
+        // take the pixel path.
+        for (int t0 = t_begin; t0 < t_end; t0 += 32) {
+            const int tw = t0 + lane;
+            bool slow_word = tw < t_end;
+            unsigned int key = 0xfffffffeu - lane;                       // matches nobody
+            if (SSB_STRIP_WORD_FAST == 1) look = look_ahead(t0);
+            if (look.n_px) {
+                const unsigned int lab0 = (look.v[0] >> (8 * look.off)) & 0xffu;
+                const unsigned int rep = lab0 * 0x01010101u;
+                unsigned int diff = 0u;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const unsigned int px4 = __funnelshift_r(look.v[j], look.v[j + 1], 8 * look.off);
+                    const int live_bytes = static_cast<int>(look.n_px) - 4 * j;
+                    const unsigned int m = live_bytes >= 4 ? 0xffffffffu : live_bytes <= 0 ? 0u : (1u << (8 * live_bytes)) - 1u;
+                    diff |= (px4 ^ rep) & m;
+                }
+                if (diff == 0u) {
+                    slow_word = false;
+                    int ly, seg;
+                    k.split(tw, ly, seg);
+                    const unsigned int row = k.lid[ly * rw + ((look.starts & 1u) ? seg * 32 : static_cast<int>(k.open[tw]))];
+                    if (row != 0xFFFFu && lab0 < static_cast<unsigned int>(p.C)) {
+                        if (look.n_px == 32u) key = (row << 8) | lab0;
+                        else add_hist(row, lab0, look.n_px);             // a row's last, shorter word
+                    }
+                }
+            }
+            if (SSB_STRIP_WORD_FAST == 2) look = look_ahead(t0 + 32);
+            const unsigned int peers = __match_any_sync(0xffffffffu, key);
+            if (key < 0xffffff00u && lane == __ffs(peers) - 1) add_hist(key >> 8, key & 0xffu, 32u * __popc(peers));
+            unsigned int slow = __ballot_sync(0xffffffffu, slow_word);
+            if (slow) {
+                int ly, seg, nly = 0, nseg = 0;
+                int wi = __ffs(slow) - 1;
+                slow &= slow - 1;
+                k.split(t0 + wi, ly, seg);
+                int lab = label_of(ly, seg);
+                while (true) {
+                    const int nwi = slow ? __ffs(slow) - 1 : -1;         // the next word's labels are requested first
+                    int nlab = 0;
+                    if (nwi >= 0) {
+                        slow &= slow - 1;
+                        k.split(t0 + nwi, nly, nseg);
+                        nlab = label_of(nly, nseg);
+                    }
+                    step(t0 + wi, ly, seg, lab);
+                    if (nwi < 0) break;
+                    wi = nwi; ly = nly; seg = nseg; lab = nlab;
+                }
+            }
         }
+#else
+        // every word takes the pixel path, the label bytes of the next three words already requested
+        {
+            int t = t_begin, ly, seg;
+            k.split(t < tasks ? t : 0, ly, seg);
+            int l_t = t, l_ly = ly, l_seg = seg;
+            auto load_label = [&]() -> int {
+                const int v = l_t < t_end ? label_of(l_ly, l_seg) : 0;
+                ++l_t;
+                if (++l_seg == S) { l_seg = 0; ++l_ly; }
+                return v;
+            };
+            auto advance = [&]() { ++t; if (++seg == S) { seg = 0; ++ly; } };
+            int la = load_label(), lb = load_label(), lc = load_label();
+            while (t < t_end) {
+                step(t, ly, seg, la); advance(); la = load_label();
+                if (t >= t_end) break;
+                step(t, ly, seg, lb); advance(); lb = load_label();
+                if (t >= t_end) break;
+                step(t, ly, seg, lc); advance(); lc = load_label();
+            }
+        }
+#endif
         flush_cache();
     }
     __syncthreads();

@@ -38,8 +38,13 @@ def main():
     field[torch.rand((b, 33, 33), device="cuda", generator=g) < 0.7] = 0
     lab = field.repeat_interleave(16, 1).repeat_interleave(16, 2)[:, :H, :W].to(torch.uint8).contiguous()
     noise = torch.randint(0, C, (b, H, W), dtype=torch.uint8, device="cuda", generator=g)
-    cases = os.environ.get("BLOBS_CASES", "blobby,noise").split(",")
-    for name, lm in (("blobby", lab), ("noise", noise)):
+    # what a segmentation network gives: a few large objects (96-pixel cells, half of them person / car)
+    big = torch.randint(1, C, (b, 7, 7), device="cuda", generator=g)
+    big[torch.rand((b, 7, 7), device="cuda", generator=g) < 0.5] = 0
+    big[torch.rand((b, 7, 7), device="cuda", generator=g) < 0.25] = 15
+    large = big.repeat_interleave(96, 1).repeat_interleave(96, 2)[:, 40:H + 40, 50:W + 50].to(torch.uint8).contiguous()
+    cases = os.environ.get("BLOBS_CASES", "blobby,noise,large").split(",")
+    for name, lm in (("blobby", lab), ("noise", noise), ("large", large)):
         if name not in cases:
             continue
         mask = ssb200.foreground_mask(lm, ROI_H, ROI_W)

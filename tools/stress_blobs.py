@@ -23,3 +23,19 @@ for (B,H,W,rh,rw,rows) in ((300,200,257,200,257,512),(1,513,513,513,513,4096),(1
     mask=ssb200.foreground_mask(lab,rh,rw)
     a=tables(mask,lab,rh,rw,rows,"cluster"); c=tables(mask,lab,rh,rw,rows,"global")
     print(B,H,W,rh,rw,rows,"regions/frame %.0f"%a["count"].mean(),"same:",same(a,c,rows),flush=True)
+# label maps with long uniform stretches (the whole-word path of the label counts), cell sizes 8..100, label maps that
+# start at every byte phase, ROIs narrower than the frame
+for i, (B,H,W,rh,rw,rows,cell) in enumerate(((64,513,513,288,513,1024,16),(64,513,513,288,513,1024,40),(40,513,513,513,513,2048,100),
+                                              (33,300,515,300,515,1024,32),(50,257,390,200,333,700,24),(20,120,1030,120,1030,900,64),
+                                              (16,513,513,288,513,1024,600),(31,97,64,97,64,300,8),(25,64,31,64,31,100,5))):
+    off=i%4
+    buf=torch.zeros(B*H*W+8,dtype=torch.uint8,device="cuda")
+    lab=buf[off:off+B*H*W].view(B,H,W)
+    cells=torch.randint(0,21,(B,H//cell+2,W//cell+2),device="cuda",generator=g)
+    cells[torch.rand(cells.shape,device="cuda",generator=g)<0.5]=15
+    cells[torch.rand(cells.shape,device="cuda",generator=g)<0.3]=0
+    lab.copy_(cells.repeat_interleave(cell,1).repeat_interleave(cell,2)[:,3:H+3,5:W+5].to(torch.uint8))
+    lab[:, ::37, ::29]=7                       # single odd pixels inside the uniform stretches
+    mask=ssb200.foreground_mask(lab,rh,rw)
+    a=tables(mask,lab,rh,rw,rows,"cluster"); c=tables(mask,lab,rh,rw,rows,"global")
+    print("cells",cell,B,H,W,rh,rw,rows,"phase",off,"regions/frame %.0f"%a["count"].mean(),"same:",same(a,c,rows),flush=True)
