@@ -445,6 +445,28 @@ def test_fg_mask_random_maps_and_rois(ssb, shape, roi):
         assert (mask == cport.fg_mask(lm, roi[0], roi[1], cm)).all()
 
 
+@pytest.mark.parametrize("shape,roi", [((2, 80, 513), (80, 513)), ((1, 75, 520), (75, 519)), ((1, 75, 521), (75, 521)),
+                                       ((2, 150, 260), (149, 258)), ((1, 30, 130), (30, 129)), ((1, 30, 131), (30, 2)),
+                                       ((1, 77, 256), (77, 253)), ((1, 77, 256), (76, 254)), ((1, 77, 256), (77, 255)),
+                                       ((1, 77, 256), (2, 256)), ((1, 40, 7), (40, 7)), ((1, 145, 384), (145, 129)),
+                                       ((1, 74, 300), (73, 128)), ((3, 513, 513), (288, 512))])
+def test_fg_mask_strip_and_roi_borders(ssb, shape, roi):
+    """Frame widths with and without narrow last columns (W mod 128 <= 8), ROIs whose last column falls on each of a
+    lane's four pixels and on strip borders, two-column and two-row ROIs; the output buffer starts as garbage (zeros
+    outside the ROI are the kernel's job)."""
+    rng = np.random.default_rng(shape[2] * 5 + roi[1])
+    cm = sp.pascal_colormap().astype(np.uint8)
+    for kind in range(2):
+        if kind == 0:
+            lm = rng.choice([0, 7, 15, 12, 20], size=shape).astype(np.uint8)
+        else:
+            small = rng.choice([0, 7, 15, 12], size=(shape[0], shape[1] // 5 + 1, shape[2] // 5 + 1))
+            lm = np.kron(small, np.ones((1, 5, 5), int))[:, :shape[1], :shape[2]].astype(np.uint8)
+        out = torch.full(shape, 0xAB, dtype=torch.uint8, device="cuda")
+        ssb.foreground_mask(torch.from_numpy(lm).cuda(), roi[0], roi[1], out=out)
+        assert (out.cpu().numpy() == cport.fg_mask(lm, roi[0], roi[1], cm)).all()
+
+
 def test_fg_mask_colours_outside_the_packed_range(ssb):
     """Labels >= 64 have colours that are not multiples of 64 (and a caller may pass any colormap): those
     box sums are recomputed from the colormap bytes."""

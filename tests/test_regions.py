@@ -278,3 +278,44 @@ def test_gpu_regions_wide_roi_and_many_rows():
                 assert (t[name][b, :count][order] == want).all(), (H, W, b, name)
             holes = (flags & 3) == 0
             assert (t["ring"][b, :count][order][holes] == ring[holes]).all(), (H, W, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", ["cluster", "global"])
+def test_gpu_regions_uniform_stretches_at_every_byte_phase(path, monkeypatch):
+    """Label maps made of large one-label cells (words that are counted whole by the cluster kernel), with single odd
+    pixels inside the stretches, rows whose last word is short, and label maps that start at byte phases 0..3."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import ssb200
+    monkeypatch.setenv("SSB_BLOB_PATH", path)
+    rng = np.random.default_rng(33)
+    for case, (H, W, roi_h, roi_w, cell) in enumerate(((150, 257, 150, 257, 40), (96, 330, 90, 301, 64), (130, 160, 130, 160, 16),
+                                                       (77, 515, 77, 515, 100), (64, 96, 64, 96, 32), (120, 131, 120, 131, 24))):
+        B = 4
+        cells = rng.choice([0, 15, 7, 3, 12], size=(B, H // cell + 2, W // cell + 2), p=[.3, .35, .15, .1, .1]).astype(np.uint8)
+        labs = np.repeat(np.repeat(cells, cell, 1), cell, 2)[:, 3:H + 3, 5:W + 5].copy()
+        labs[:, ::17, ::23] = 7
+        labs[:, 5::29, 7::31] = 0
+        labs[3] = 15 if case % 2 else 0
+        masks = np.zeros_like(labs)
+        for b in range(B):
+            masks[b, :roi_h, :roi_w] = sp.foreground_mask(labs[b, :roi_h, :roi_w])
+        phase = case % 4
+        buf = torch.zeros(B * H * W + 8, dtype=torch.uint8, device="cuda")
+        lab_d = buf[phase:phase + B * H * W].view(B, H, W)
+        lab_d.copy_(torch.from_numpy(labs))
+        assert lab_d.data_ptr() % 4 == phase
+        t = ssb200.blob_regions(torch.from_numpy(masks).cuda(), lab_d, roi_h, roi_w, 21, 2048)
+        torch.cuda.synchronize()
+        t = {k: v.cpu().numpy() for k, v in t.items()}
+        for b in range(B):
+            count, first, parent, flags, hist, ring = scipy_table(masks[b, :roi_h, :roi_w], labs[b, :roi_h, :roi_w])
+            assert t["count"][b] == count, (case, b)
+            order = np.argsort(t["first"][b, :count])
+            for name, want in (("first", first), ("parent", parent), ("flags", flags), ("hist", hist)):
+                assert (t[name][b, :count][order] == want).all(), (case, b, name)
+            holes = (flags & 3) == 0
+            assert (t["ring"][b, :count][order][holes] == ring[holes]).all(), (case, b)
+            assert int(t["hist"][b, :count].sum()) == roi_h * roi_w
