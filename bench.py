@@ -455,7 +455,7 @@ def reply_e2e(ssb200, torch, n_frames=2048, batch=64, contour_stage=None):
     engine = FixedScores(torch, batch)
     names = {i: "label%d" % i for i in range(C)}
     rates = []
-    for n in (4 * batch, n_frames, n_frames, n_frames):   # first pass: allocations, thread pools, lazy module loads
+    for n in (4 * batch,) + (n_frames,) * 5:               # first pass: allocations, thread pools, lazy module loads
         camera = srv.ArrayCamera([cam[i % 8] for i in range(n)])
         t0 = time.perf_counter()
         srv.recognize_and_segment(True, camera, engine, names, 0.05, batch_frames=batch, mode="contours",
