@@ -33,6 +33,7 @@ constexpr int kRootListCap = 2048;    // strip-local roots kept in a list (more:
 //                                 region, the common labels) queue up in L2
 //   bar   one mbarrier (staging copy)
 constexpr int kHistRows = 16;
+constexpr int kWordLabels = 4;        // a one-run word with up to this many labels is counted by one lane (label counts)
 struct StripLayout {
     int bits, st, open, lid, list, hk, bar, total;
 };
@@ -648,33 +649,57 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
             return x < rw ? lab_f[static_cast<long long>(y0 + ly) * p.W + x] : 0;
         };
 #if SSB_STRIP_WORD_FAST
-        // 32 words at a time, first a LANE per word: a candidate word whose pixels all carry one label is counted by
-        // its lane alone -- words of the same (row, label) among the 32 by one lane for all.  The other words then
-        // take the pixel path.
+        // 32 words at a time, first a LANE per word: a candidate word whose pixels carry at most kWordLabels labels is
+        // counted by its lane alone -- one-label words of the same (row, label) among the 32 by one lane for all.
+        // The other words then take the pixel path.
         for (int t0 = t_begin; t0 < t_end; t0 += 32) {
             const int tw = t0 + lane;
             bool slow_word = tw < t_end;
             unsigned int key = 0xfffffffeu - lane;                       // matches nobody
             if (SSB_STRIP_WORD_FAST == 1) look = look_ahead(t0);
             if (look.n_px) {
-                const unsigned int lab0 = (look.v[0] >> (8 * look.off)) & 0xffu;
-                const unsigned int rep = lab0 * 0x01010101u;
-                unsigned int diff = 0u;
+                // The word's pixels by label, up to kWordLabels labels: the label of the first pixel not yet
+                // accounted for, the pixels that carry it (XOR, top bit of every non-zero byte, four bits gathered
+                // by one multiply), until none is left.  A word with more labels takes the pixel path.
+                unsigned int w[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const unsigned int px4 = __funnelshift_r(look.v[j], look.v[j + 1], 8 * look.off);
-                    const int live_bytes = static_cast<int>(look.n_px) - 4 * j;
-                    const unsigned int m = live_bytes >= 4 ? 0xffffffffu : live_bytes <= 0 ? 0u : (1u << (8 * live_bytes)) - 1u;
-                    diff |= (px4 ^ rep) & m;
+                for (int j = 0; j < 8; ++j) w[j] = __funnelshift_r(look.v[j], look.v[j + 1], 8 * look.off);
+                int ly, seg;
+                k.split(tw, ly, seg);
+                const uint8_t *lab_row = lab_f + static_cast<long long>(y0 + ly) * p.W + seg * 32;
+                unsigned int left = look.n_px == 32u ? 0xffffffffu : (1u << look.n_px) - 1u;   // pixels not yet accounted for
+                unsigned int labs[kWordLabels], cnts[kWordLabels];
+#pragma unroll
+                for (int r = 0; r < kWordLabels; ++r) {
+                    labs[r] = 0u;
+                    cnts[r] = 0u;
+                    if (left && !(r >= 2 && __popc(left) > 8)) {          // two labels gone and a quarter still open: give up
+                        const unsigned int lab_r = r == 0 ? (w[0] & 0xffu) : lab_row[__ffs(left) - 1];
+                        const unsigned int rep = lab_r * 0x01010101u;
+                        unsigned int other = 0u;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const unsigned int x4 = w[j] ^ rep;
+                            const unsigned int top = (((x4 & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x4) & 0x80808080u;
+                            other |= (((top >> 7) * 0x01020408u) >> 24) << (4 * j);
+                        }
+                        const unsigned int same = left & ~other;
+                        labs[r] = lab_r;
+                        cnts[r] = __popc(same);
+                        left &= other;
+                    }
                 }
-                if (diff == 0u) {
+                if (left == 0u) {
                     slow_word = false;
-                    int ly, seg;
-                    k.split(tw, ly, seg);
                     const unsigned int row = k.lid[ly * rw + ((look.starts & 1u) ? seg * 32 : static_cast<int>(k.open[tw]))];
-                    if (row != 0xFFFFu && lab0 < static_cast<unsigned int>(p.C)) {
-                        if (look.n_px == 32u) key = (row << 8) | lab0;
-                        else add_hist(row, lab0, look.n_px);             // a row's last, shorter word
+                    if (row != 0xFFFFu) {
+                        if (cnts[0] == 32u) {
+                            if (labs[0] < static_cast<unsigned int>(p.C)) key = (row << 8) | labs[0];
+                        } else {
+#pragma unroll
+                            for (int r = 0; r < kWordLabels; ++r)
+                                if (cnts[r] && labs[r] < static_cast<unsigned int>(p.C)) add_hist(row, labs[r], cnts[r]);
+                        }
                     }
                 }
             }
