@@ -12,6 +12,9 @@ constexpr int kStrips = 8;            // CTAs per cluster = horizontal strips of
 #define SSB_STRIP_WORD_FAST 1   // label counts: 0 = every word a lane per pixel; 1 = uniform words are counted by one lane each;
                                 // 2 = the same with the label bytes of the next 32 words requested one round ahead (slower)
 #endif
+#ifndef SSB_STRIP_SHARE_SLOW
+#define SSB_STRIP_SHARE_SLOW 1  // label counts: the words that take the pixel path are listed and shared by the CTA's warps
+#endif
 #ifndef SSB_STRIP_STOP
 #define SSB_STRIP_STOP 0   // tuning: n > 0 ends the kernel after its n-th phase (cumulative phase timing)
 #endif
@@ -244,7 +247,7 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
     unsigned int *hk_tag = reinterpret_cast<unsigned int *>(strip_smem + sp.L.hk), *hk_cnt = hk_tag + kHistRows;
     for (int i = tid; i < (rows + 2) * k.SW; i += kStripThreads) k.mb[i] = 0u;
     for (int i = tid; i < kHistRows * (p.C + 1); i += kStripThreads) hk_tag[i] = i < kHistRows ? 0xffffffffu : 0u;
-    if (tid == 0) *k.n_roots = 0u;
+    if (tid == 0) k.n_roots[0] = k.n_roots[1] = 0u;                     // [1]: words left to the pixel path (label counts)
     __syncthreads();
     pdl_wait();
     if (s == 0 && tid == 0) p.count[f] = 0;
@@ -586,6 +589,9 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
             cache_cnt = 0u;
         };
         const unsigned int below = 0xffffffffu >> (31 - lane);           // bits of lanes <= lane
+        // the root list is free again: it takes the words that are left to the pixel path (when they all fit)
+        const bool listed = SSB_STRIP_SHARE_SLOW && tasks <= kRootListCap;
+        unsigned int *n_slow = k.n_roots + 1;
         // one word, a lane per pixel
         auto step = [&](int t, int ly, int seg, int lab) {
             const int x = seg * 32 + lane;
@@ -707,7 +713,15 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
             const unsigned int peers = __match_any_sync(0xffffffffu, key);
             if (key < 0xffffff00u && lane == __ffs(peers) - 1) add_hist(key >> 8, key & 0xffu, 32u * __popc(peers));
             unsigned int slow = __ballot_sync(0xffffffffu, slow_word);
-            if (slow) {
+            if (listed) {
+                // the CTA's warps share the pixel-path words afterwards (a warp whose range holds many of them would
+                // keep the others waiting)
+                if (slow) {
+                    unsigned int at = lane == 0 ? atomicAdd(n_slow, static_cast<unsigned int>(__popc(slow))) : 0u;
+                    at = __shfl_sync(0xffffffffu, at, 0);
+                    if (slow_word) k.list[at + __popc(slow & ((1u << lane) - 1u))] = static_cast<unsigned short>(tw);
+                }
+            } else if (slow) {
                 int ly, seg, nly = 0, nseg = 0;
                 int wi = __ffs(slow) - 1;
                 slow &= slow - 1;
@@ -725,6 +739,27 @@ __global__ void __launch_bounds__(kStripThreads, SSB_STRIP_MIN_CTAS) blob_cluste
                     if (nwi < 0) break;
                     wi = nwi; ly = nly; seg = nseg; lab = nlab;
                 }
+            }
+        }
+        if (listed) {
+            __syncthreads();
+            const int n_listed = static_cast<int>(*n_slow);
+            int i = warp, ly = 0, seg = 0, lab = 0, t = 0;
+            if (i < n_listed) {
+                t = k.list[i];
+                k.split(t, ly, seg);
+                lab = label_of(ly, seg);
+            }
+            while (i < n_listed) {
+                const int ni = i + kStripWarps;                          // the next word's labels are requested first
+                int nt = 0, nly = 0, nseg = 0, nlab = 0;
+                if (ni < n_listed) {
+                    nt = k.list[ni];
+                    k.split(nt, nly, nseg);
+                    nlab = label_of(nly, nseg);
+                }
+                step(t, ly, seg, lab);
+                i = ni; t = nt; ly = nly; seg = nseg; lab = nlab;
             }
         }
 #else
