@@ -242,17 +242,22 @@ def test_candidates_from_tables_and_moments_equal_the_border_following():
 
 
 @pytest.mark.gpu
-def test_gpu_contour_moments_give_the_border_following_candidates():
+@pytest.mark.parametrize("path", ["bits", "warp"])
+def test_gpu_contour_moments_give_the_border_following_candidates(path, monkeypatch):
     """Mask kernel -> region tables -> contour integrals on the GPU -> candidates, against the border following with
-    marks on the same masks (which equals OpenCV): every frame that does not ask for the masks must agree exactly."""
+    marks on the same masks (which equals OpenCV): every frame that does not ask for the masks must agree exactly.
+    Both kernels behind ssb_contour_moments_u8: bit rows in shared memory with a thread per table row (the default),
+    and a warp per table row on the mask bytes."""
     torch = pytest.importorskip("torch")
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     import ssb200
     from oracle import segpath as sp
+    monkeypatch.setenv("SSB_MOMENTS_PATH", path)
     rng = np.random.default_rng(77)
     checked = asked = 0
-    for (B, H, W, roi_h, roi_w) in ((24, 96, 130, 96, 130), (16, 513, 513, 288, 513), (12, 64, 80, 50, 77)):
+    for (B, H, W, roi_h, roi_w) in ((24, 96, 130, 96, 130), (16, 513, 513, 288, 513), (12, 64, 80, 50, 77), (6, 70, 131, 70, 128),
+                                  (5, 40, 35, 33, 32)):
         labs = np.zeros((B, H, W), np.uint8)
         for i in range(B):
             if i % 3 == 2:

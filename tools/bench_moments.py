@@ -16,7 +16,14 @@ def main():
     field[field > 0] = torch.where(torch.rand(int((field > 0).sum()), device="cuda", generator=g) < 0.5, 15, 7)
     big = field.repeat_interleave(64, 1).repeat_interleave(64, 2)[:, :H, :W].to(torch.uint8).contiguous()
     noise = torch.randint(0, 21, (b, H, W), dtype=torch.uint8, device="cuda", generator=g)
-    for name, lab in (("64-px cells", big), ("noise", noise)):
+    cells16 = torch.randint(1, 21, (b, 33, 33), device="cuda", generator=g)
+    cells16[torch.rand((b, 33, 33), device="cuda", generator=g) < 0.7] = 0
+    blobby = cells16.repeat_interleave(16, 1).repeat_interleave(16, 2)[:, :H, :W].to(torch.uint8).contiguous()
+    one = torch.zeros((1, H, W), dtype=torch.uint8, device="cuda")
+    one[0, 20:270, 30:480] = 15
+    one[0, 60:230, 90:420] = 0
+    for name, lab in (("64-px cells", big), ("16-px cells", blobby), ("noise", noise), ("1 frame, ring", one)):
+        b = lab.shape[0]
         mask = ssb200.foreground_mask(lab, rh, rw)
         t = ssb200.blob_regions(mask, lab, rh, rw, 21, 1024)
         for _ in range(3):
