@@ -204,7 +204,8 @@ SSB_API int ssb_blob_regions_u8(const uint8_t *mask, const uint8_t *labels, int 
  *   moments [B][max_regions][3] i64 = a00, a10, a01:  contourArea = |a00| / 2,  m00 = a00 / 2,  m10 = a10 / 6,
  *   m01 = a01 / 6 (sign of a00 folded in, as OpenCV does) -- exact integers, so the doubles formed from them equal
  *   OpenCV's.  Rows of the outside background and rows at or beyond count[b] (or beyond max_regions) are zero /
- *   not written.  `mask` is the array the table was made from; same ROI.  A warp per row walks the border; a border
+ *   not written.  `mask` is the array the table was made from; same ROI.  A thread per row walks the border on bit
+ *   planes of the frame's mask held in shared memory (a warp per row on the mask bytes where they do not fit); a border
  *   longer than 32 768 steps is given up (bounded GPU time) and its row marked a00 = 0, a10 = INT64_MIN:
  *   ssb_candidates_from_moments_host then reports the frame with n_candidates = -1. */
 SSB_API int ssb_contour_moments_u8(const uint8_t *mask, int B, int H, int W, int roi_h, int roi_w, int max_regions,
