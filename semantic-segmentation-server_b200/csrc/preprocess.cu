@@ -4,9 +4,9 @@
 //
 // One WARP per (frame, output row), two independent warps per CTA, no block-wide barriers:
 //   1. the sampled source row (Wc*3 bytes, 5760 B at 1080p) is copied into the warp's shared memory
-//      with 16-byte cp.async transfers -- every 32-byte sector of a sampled row is touched by the
-//      11.2-byte sample stride anyway, so reading the row densely costs no extra DRAM traffic and
-//      makes the read side fully vectorised and coalesced;
+//      by ONE bulk async copy (cp.async.bulk, completion on the warp's own mbarrier; plain loads for
+//      a ragged head / tail) -- every 32-byte sector of a sampled row is touched by the 11.2-byte
+//      sample stride anyway, so reading the row densely costs no extra DRAM traffic;
 //   2. each lane gathers quads of pixels (source offsets from the host-built Pillow index table, one
 //      128-bit load per quad, issued while the row copy is still in flight: the kernel is bound by
 //      the chain table load -> row copy -> gather -> store of a warp, not by bytes), swaps B and R
@@ -37,6 +37,9 @@ constexpr int kPrePrefetch = 5;   // quads per lane whose table entries are pref
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem_dst)), "l"(gmem_src) : "memory");
 }
+#ifndef SSB_PRE_BULK
+#define SSB_PRE_BULK 1      // 1: the 16-byte aligned middle of a row is ONE bulk async copy per warp; 0: 16-byte cp.async per lane
+#endif
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 template <bool kStore32>
@@ -77,8 +80,24 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
     const int head = min(row_bytes, (16 - sphase) & 15);
     const int body16 = (row_bytes - head) >> 4;
     uint8_t *sp = src + sphase;
+#if SSB_PRE_BULK
+    // the 16-byte aligned middle of the row as ONE bulk async copy (UBLKCP) issued by lane 0, completion on the warp's
+    // own mbarrier (a dozen 16-byte cp.async per lane took 16 % of the kernel's instructions)
+    __shared__ uint64_t row_bar[kPreWarps];
+    if (lane == 0) {
+        mbar_init(&row_bar[warp], 1);
+        mbar_init_fence();
+        if (body16 > 0) {
+            mbar_arrive_expect_tx(&row_bar[warp], static_cast<uint32_t>(body16) * 16u);
+            bulk_copy_g2s_plain(sp + head, srow + head, static_cast<uint32_t>(body16) * 16u, &row_bar[warp]);
+        }
+    }
+    __syncwarp();
+    for (int i = lane; i < head; i += 32) sp[i] = srow[i];
+#else
     for (int i = lane; i < head; i += 32) sp[i] = srow[i];
     for (int i = lane; i < body16; i += 32) cp_async16(sp + head + i * 16, srow + head + i * 16);
+#endif
     for (int i = head + body16 * 16 + lane; i < row_bytes; i += 32) sp[i] = srow[i];
     // the index-table entries of this lane's first quads are fetched while the row is in flight
     const int quads = (W + 3) >> 2;
@@ -88,7 +107,11 @@ preprocess_nearest_kernel(const uint8_t *__restrict__ frames, long long frame_st
         const int x0 = (lane + 32 * k) * 4;
         pre[k] = x0 + 3 < new_w ? *reinterpret_cast<const int4 *>(xtab + x0) : make_int4(0, 0, 0, 0);   // 16-byte aligned table
     }
+#if SSB_PRE_BULK
+    if (body16 > 0) mbar_wait(&row_bar[warp], 0);
+#else
     cp_async_wait_all();
+#endif
     __syncwarp();
 #if SSB_PRE_TRIGGER == 2
     pdl_trigger();   // this warp's reads are done
