@@ -200,6 +200,102 @@ def _row_moments(mask, first, flags):
     return out
 
 
+def _row_moments_with_stretches(mask, first, flags):
+    """CPU twin of the default kernel behind ssb_contour_moments_u8 (contour_moments_bits_kernel): the same walk, but a
+    straight horizontal or vertical stretch is taken in one step -- the walk goes on eastwards from a pixel q iff SW, S,
+    SE of q are background and E is foreground (W: NE, N, NW, W; S: NW, W, SW, S; N: SE, E, NE, N), at most 30 pixels at
+    a time, never past (x1, y1).  Returns the sums and how many steps were saved."""
+    h, w = mask.shape
+    dx, dy = [1, 1, 0, -1, -1, -1, 0, 1], [0, -1, -1, -1, 0, 1, 1, 1]
+
+    def fg(x, y):
+        return 0 <= x < w and 0 <= y < h and mask[y, x] != 0
+    out = np.zeros((len(first), 3), np.int64)
+    saved = 0
+    for r, (fp, fl) in enumerate(zip(first.tolist(), (flags & 3).tolist())):
+        if fl == 2:
+            continue
+        hole = fl == 0
+        y0, x0 = divmod(fp, w)
+        x0 -= 1 if hole else 0
+        s_end = s = 0 if hole else 4
+        while True:
+            s = (s - 1) & 7
+            if fg(x0 + dx[s], y0 + dy[s]) or s == s_end:
+                break
+        if not fg(x0 + dx[s], y0 + dy[s]):
+            continue
+        x1, y1, x, y, pts, travel = x0 + dx[s], y0 + dy[s], x0, y0, [], -1
+        while True:
+            while True:
+                s += 1
+                nx, ny = x + dx[s & 7], y + dy[s & 7]
+                if fg(nx, ny):
+                    break
+            s &= 7
+            pts.append((x, y))
+            if (nx, ny) == (x0, y0) and (x, y) == (x1, y1):
+                break
+            x, y = nx, ny
+            if s == travel and s % 2 == 0:
+                ux, uy = dx[s], dy[s]                                  # unit step of the stretch
+                # the side that must stay background: below when going east, above (west), left (south), right (north)
+                sx, sy = {0: (0, 1), 4: (0, -1), 6: (-1, 0), 2: (1, 0)}[s]
+                n = 0
+                while n < 30:
+                    qx, qy = x + n * ux, y + n * uy
+                    side_clear = not any(fg(qx + sx + k * ux, qy + sy + k * uy) for k in (-1, 0, 1))
+                    if not (side_clear and fg(qx + ux, qy + uy)):
+                        break
+                    n += 1
+                # never past (x1, y1): the walk may end there
+                for k in range(n + 1):
+                    if (x + k * ux, y + k * uy) == (x1, y1):
+                        n = k
+                        break
+                x, y = x + n * ux, y + n * uy
+                saved += n
+            travel = s
+            s = (s + 4) & 7
+        px, py = pts[-1]
+        for x, y in pts:
+            d = px * y - x * py
+            out[r] += (d, d * (px + x), d * (py + y))
+            px, py = x, y
+    return out, saved
+
+
+def test_straight_stretches_in_one_step_leave_the_contour_sums_unchanged():
+    """The rule the GPU walk uses to take straight stretches in one step, on noise, blocky masks (long stretches), masks
+    whose regions touch the ROI border, one-pixel lines and rings: same a00 / a10 / a01 as the pixel-by-pixel walk."""
+    rng = np.random.default_rng(5)
+    H, W = 48, 70
+    rows = saved = 0
+    for rep in range(40):
+        if rep % 4 == 0:
+            masks = _random_masks(rng, 4, H, W, rep)
+        else:
+            cell = (2, 3, 5, 8, 13)[rep % 5]
+            small = rng.random((4, H // cell + 1, W // cell + 1)) < (0.35 + 0.1 * (rep % 3))
+            masks = (np.kron(small, np.ones((1, cell, cell), bool))[:, :H, :W] * 255).astype(np.uint8)
+            if rep % 8 == 1:
+                masks[:, 0, :] = 255                       # a one-pixel line along the ROI's top row
+                masks[:, :, W - 1] = 255
+            if rep % 8 == 3:
+                masks[0] = 0
+                masks[0, 4:44, 5:65] = 255                 # a ring with a one-pixel wall between two holes
+                masks[0, 8:40, 9:34] = 0
+                masks[0, 8:40, 35:61] = 0
+        for i in range(len(masks)):
+            n, f, p, fl, _, _ = scipy_table(masks[i], np.zeros_like(masks[i]))
+            want = _row_moments(masks[i], f, fl)
+            got, s = _row_moments_with_stretches(masks[i], f, fl)
+            assert (got == want).all(), (rep, i)
+            rows += n
+            saved += s
+    assert rows > 2000 and saved > 20000, (rows, saved)
+
+
 def test_candidates_from_tables_and_moments_equal_the_border_following():
     """Region tables + contour integrals -> the candidate list (order, flags, keys, areas, centroids) the border
     following with marks gives on the mask; frames where two holes of one region are candidates ask for the masks."""
