@@ -292,7 +292,8 @@ def test_gpu_regions_uniform_stretches_at_every_byte_phase(path, monkeypatch):
     monkeypatch.setenv("SSB_BLOB_PATH", path)
     rng = np.random.default_rng(33)
     for case, (H, W, roi_h, roi_w, cell) in enumerate(((150, 257, 150, 257, 40), (96, 330, 90, 301, 64), (130, 160, 130, 160, 16),
-                                                       (77, 515, 77, 515, 100), (64, 96, 64, 96, 32), (120, 131, 120, 131, 24))):
+                                                       (77, 515, 77, 515, 100), (64, 96, 64, 96, 32), (120, 131, 120, 131, 24),
+                                                       (728, 720, 728, 720, 56))):     # more words per strip than the shared list holds
         B = 4
         cells = rng.choice([0, 15, 7, 3, 12], size=(B, H // cell + 2, W // cell + 2), p=[.3, .35, .15, .1, .1]).astype(np.uint8)
         labs = np.repeat(np.repeat(cells, cell, 1), cell, 2)[:, 3:H + 3, 5:W + 5].copy()
