@@ -178,7 +178,10 @@ SSB_API int ssb_fg_mask_u8(const uint8_t *labels, int B, int H, int W, int roi_h
  * the enclosure tree (Python: ssb200.objects_from_regions); polygon area and moments (:93, :115)
  * stay with OpenCV.
  *
- *   mask, labels [B][H][W] u8 (ssb_fg_mask_u8 / ssb_argmax_stats_* outputs); label values >= C are not counted
+ *   mask, labels [B][H][W] u8 (ssb_fg_mask_u8 / ssb_argmax_stats_* outputs); label values >= C are not counted.
+ *                Both are read as aligned 32-bit words: the words that hold a frame's first and last ROI byte are
+ *                read whole (up to 3 bytes either side, never across a 4-byte boundary of its own -- inside any
+ *                CUDA allocation); the same holds for `mask` in ssb_contour_moments_u8
  *   scratch      ssb_blob_regions_scratch_bytes(B, roi_h, roi_w) bytes of device memory, contents ignored
  *   count        [B] regions found; a frame with count > max_regions has an incomplete table (use the
  *                per-contour fill for that frame)
