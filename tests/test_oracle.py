@@ -199,3 +199,41 @@ def test_per_label_objects_formulas():
     assert o["score"] == 1.0 and abs(o["score_conf"] - 0.5 * (250 - 128)) < 1e-12
     allobjs = sp.per_label_objects(stats, 513, 513, names, 0.0, only_foreground=False)
     assert [o["label_index"] for o in allobjs] == [15, 12, 7, 3]
+
+
+def test_packed_box_sum_indexes_the_threshold_table():
+    """The arithmetic of the mask kernel (csrc/fgmask.cu) restated in numpy against the oracle: a colour whose channels
+    are multiples of 64 becomes one 15-bit code (c/64 in three 5-bit fields), two pixels share a 32-bit word (16 bits
+    each), the 3 x 3 box sum of the words never carries from one field (or pixel) into the next, and the sum itself
+    indexes the tables -- t01[sum & 1023] >= t2[sum >> 10]  <=>  gray > 127."""
+    rng = np.random.default_rng(12)
+    cm = sp.pascal_colormap().astype(np.uint8)
+    assert not (cm[:64] & 63).any()                       # what the packed path relies on for the first 64 labels
+    code = (cm[:, 0].astype(np.uint32) >> 6) | (cm[:, 1].astype(np.uint32) >> 6) << 5 | (cm[:, 2].astype(np.uint32) >> 6) << 10
+    mean = (2 * 64 * np.arange(32) + 9) // 18
+    t01 = (1868 * mean)[None, :] + (9617 * mean)[:, None]           # [s1][s0]
+    t2 = (128 << 14) - 8192 - 4899 * mean
+    for shape, roi in (((3, 40, 70), (40, 70)), ((2, 33, 64), (20, 63)), ((1, 9, 5), (9, 5)), ((2, 30, 31), (30, 2))):
+        for kind in range(2):
+            if kind == 0:
+                lm = rng.integers(0, 64, shape).astype(np.uint8)
+            else:
+                small = rng.choice([0, 7, 15, 12, 63], size=(shape[0], shape[1] // 4 + 1, shape[2] // 4 + 1))
+                lm = np.kron(small, np.ones((1, 4, 4), int))[:, :shape[1], :shape[2]].astype(np.uint8)
+            want = cport.fg_mask(lm, roi[0], roi[1], cm)
+            for b in range(shape[0]):
+                if min(roi) < 2:
+                    continue                                         # one-column / one-row ROIs take the plain formula
+                cpad = np.pad(code[lm[b, :roi[0], :roi[1]]], 1, mode="reflect")      # BORDER_REFLECT_101 at the ROI border
+                box = sum(cpad[dy:dy + roi[0], dx:dx + roi[1]] for dy in range(3) for dx in range(3))
+                assert ((box & 31) <= 27).all() and ((box >> 5 & 31) <= 27).all() and (box >> 15 == 0).all()   # no carries
+                # two pixels per 32-bit word, as the kernel holds them: nine packed words summed give the two box sums
+                c2 = np.pad(cpad, ((0, 0), (0, cpad.shape[1] % 2)))
+                words = c2[:, 0::2] | c2[:, 1::2] << 16
+                assert words.dtype == np.uint32
+                wsum = words[0:-2] + words[1:-1] + words[2:]                        # vertical 3-sums of packed words
+                v = cpad[0:-2] + cpad[1:-1] + cpad[2:]
+                v = np.pad(v, ((0, 0), (0, v.shape[1] % 2)))
+                assert ((wsum & 0xffff) == v[:, 0::2]).all() and ((wsum >> 16) == v[:, 1::2]).all()
+                lit = t01[(box >> 5) & 31, box & 31] >= t2[box >> 10]
+                assert (np.where(lit, 255, 0) == want[b, :roi[0], :roi[1]]).all(), (shape, roi, kind, b)
