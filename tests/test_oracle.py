@@ -237,3 +237,30 @@ def test_packed_box_sum_indexes_the_threshold_table():
                 assert ((wsum & 0xffff) == v[:, 0::2]).all() and ((wsum >> 16) == v[:, 1::2]).all()
                 lit = t01[(box >> 5) & 31, box & 31] >= t2[box >> 10]
                 assert (np.where(lit, 255, 0) == want[b, :roi[0], :roi[1]]).all(), (shape, roi, kind, b)
+
+
+def test_byte_to_bit_gather_used_by_the_region_and_contour_kernels():
+    """The word arithmetic csrc/blobs_cluster.cuh and csrc/contours.cu use to turn four mask bytes into four bits and to
+    count a word's pixels by label, restated on numpy uint32: top bit of every non-zero byte, then one multiply by
+    0x01020408 gathers the four top bits into bits 24..27 (no two partial products meet in those bits)."""
+    rng = np.random.default_rng(4)
+    px4 = rng.integers(0, 2 ** 32, 20000, dtype=np.uint64).astype(np.uint32)
+    px4[rng.random(px4.size) < 0.5] &= np.uint32(0x00ff00ff)          # plenty of zero bytes
+    px4[rng.random(px4.size) < 0.3] &= np.uint32(0xff0000ff)
+    px4[:4] = (0, 0xffffffff, 0x01000000, 0x00000080)
+    top = (((px4 & np.uint32(0x7f7f7f7f)) + np.uint32(0x7f7f7f7f)) | px4) & np.uint32(0x80808080)
+    bits4 = ((top >> np.uint32(7)) * np.uint32(0x01020408)) >> np.uint32(24)      # uint32 arithmetic wraps like the GPU's
+    want = sum((((px4 >> np.uint32(8 * k)) & np.uint32(0xff)) != 0).astype(np.uint32) << np.uint32(k) for k in range(4))
+    assert (bits4 == want).all()
+    # pixels of a 32-pixel word that carry a given label: XOR with the replicated label, then the same gather, inverted
+    words = rng.integers(0, 3, (500, 32)).astype(np.uint8)            # three labels, long enough runs of each
+    for lab in range(3):
+        other = np.zeros(500, np.uint32)
+        for j in range(8):
+            w = words[:, 4 * j:4 * j + 4].copy().view(np.uint32)[:, 0]                   # little endian: pixel 4j in byte 0
+            x4 = w ^ np.uint32(lab * 0x01010101)
+            t = (((x4 & np.uint32(0x7f7f7f7f)) + np.uint32(0x7f7f7f7f)) | x4) & np.uint32(0x80808080)
+            other |= (((t >> np.uint32(7)) * np.uint32(0x01020408)) >> np.uint32(24)) << np.uint32(4 * j)
+        same = ~other
+        want = sum((words[:, i] == lab).astype(np.uint32) << np.uint32(i) for i in range(32))
+        assert (same == want).all()
