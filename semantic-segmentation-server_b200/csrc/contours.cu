@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(kBitsThreads) contour_moments_bits_kernel(cons
         bits[(y + 1) * SW + seg + 1] = n_px == 32 ? word : word & ((1u << n_px) - 1u);
     }
     __syncthreads();
-    // bit columns: a warp transposes a block of 32 rows x 32 columns, lane j holding row j's word: the ballot of bit b
-    // is column b's word; lane b keeps it and stores it (guards and ragged edges stay zero)
+    // bit columns: a warp transposes a block of 32 rows x 32 columns in registers, lane j holding row j's word before
+    // and column j's word after (guards and ragged edges stay zero); 32 ballots per block took ~4 us more per launch
     for (int i = tid; i < (p.roi_w + 2) * TW + 4; i += kBitsThreads) bits_t[i] = 0u;
     __syncthreads();
     if (SSB_MOMENTS_RUNS) {
@@ -168,11 +168,15 @@ __global__ void __launch_bounds__(kBitsThreads) contour_moments_bits_kernel(cons
             const int k = blk / S, w = blk - k * S;
             const int y = k * 32 + lane;
             const unsigned int word = y < p.roi_h ? bits[(y + 1) * SW + w + 1] : 0u;
-            unsigned int mine = 0u;
+            // five butterfly stages: stage j swaps the off-diagonal j x j sub-blocks with lane ^ j
+            unsigned int mine = word;
 #pragma unroll
-            for (int bcol = 0; bcol < 32; ++bcol) {
-                const unsigned int col = __ballot_sync(0xffffffffu, (word >> bcol) & 1u);
-                mine = lane == bcol ? col : mine;
+            for (int st = 0; st < 5; ++st) {
+                const int j = 16 >> st;
+                const unsigned int m = st == 0 ? 0x0000ffffu : st == 1 ? 0x00ff00ffu : st == 2 ? 0x0f0f0f0fu
+                                       : st == 3 ? 0x33333333u : 0x55555555u;
+                const unsigned int t = __shfl_xor_sync(0xffffffffu, mine, j);
+                mine = (lane & j) ? ((t >> j) & m) | (mine & ~m) : (mine & m) | ((t << j) & ~m);
             }
             const int x = w * 32 + lane;
             if (x < p.roi_w) bits_t[(x + 1) * TW + k + 1] = mine;
