@@ -346,8 +346,10 @@ def other_kernels(ssb200, torch):
     tabs = ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024)
     us_r = _time_us(torch, lambda i: ssb200.blob_regions(mask_b, lab_b, CAM_ROI_H, CAM_ROI_W, C, 1024, out=tabs), 20)
     regions = tabs["count"].float().mean().item()
-    out.append({"kernel": "fg_mask + blob_regions, blobby label maps, ROI 288x513 (batch 64)", "us_fg_mask": us_m,
-                "us_blob_regions": us_r, "frames_per_s": b / (us_m + us_r) * 1e6, "regions_per_frame": regions})
+    us_c = _time_us(torch, lambda i: ssb200.contour_moments(mask_b, tabs, CAM_ROI_H, CAM_ROI_W), 20)
+    out.append({"kernel": "fg_mask + blob_regions + contour_moments, blobby label maps, ROI 288x513 (batch 64)", "us_fg_mask": us_m,
+                "us_blob_regions": us_r, "us_contour_moments": us_c, "frames_per_s": b / (us_m + us_r + us_c) * 1e6,
+                "regions_per_frame": regions})
     del qb, field, lab_true
     # config 3 as one unit: 256 camera frames -> K1 -> model input, and the post-process of 256 frames with
     # the 16:9 crop (the class scores are synthetic: the model between the two is not part of the path)
